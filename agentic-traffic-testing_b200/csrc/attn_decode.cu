@@ -1,0 +1,319 @@
+// Paged-KV decode attention (one query token per sequence), split along the KV length.
+//
+// Arithmetic follows eager_attention_forward (transformers/models/llama/modeling_llama.py:199-222):
+// scores = q.k * head_dim**-0.5, softmax in fp32, out = P.V, with repeat_kv (:187-196) realised by
+// letting the G = Hq/Hkv query heads of one KV head share every K/V row that is read.
+//
+// Decode attention is HBM-bound integer-indexed byte streaming: grid = (Hkv, B, splits); 16 lanes
+// own one cache row (16-byte vector loads, rows of a page are contiguous so a warp reads whole
+// 128-byte lines), score reductions are 4-step warp shuffles, the online softmax state lives in
+// registers, and the next rows are already in flight (register double buffer) while the current
+// ones are consumed. Partial (max, sum, out) per split go to caller scratch and are merged by
+// attn_decode_reduce_kernel.
+#include "common.cuh"
+
+#include "../../include/atx_b200.h"
+
+namespace atx {
+
+constexpr int kDecThreads = 128;
+constexpr int kDecWarps = kDecThreads / 32;
+constexpr int kTokPerIter = kDecWarps * 2 * 2;  // warps x lane-groups x unroll
+
+template <int DL>
+struct RowVec;
+template <>
+struct RowVec<8> {
+    uint4 v;
+    __device__ __forceinline__ void load(const __nv_bfloat16* p) {
+        asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
+                     : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                     : "l"(p));
+    }
+    __device__ __forceinline__ void unpack(float (&f)[8]) const {
+        f[0] = bf16lo(v.x); f[1] = bf16hi(v.x); f[2] = bf16lo(v.y); f[3] = bf16hi(v.y);
+        f[4] = bf16lo(v.z); f[5] = bf16hi(v.z); f[6] = bf16lo(v.w); f[7] = bf16hi(v.w);
+    }
+};
+template <>
+struct RowVec<4> {
+    uint2 v;
+    __device__ __forceinline__ void load(const __nv_bfloat16* p) {
+        asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
+    }
+    __device__ __forceinline__ void unpack(float (&f)[4]) const {
+        f[0] = bf16lo(v.x); f[1] = bf16hi(v.x); f[2] = bf16lo(v.y); f[3] = bf16hi(v.y);
+    }
+};
+
+__device__ __forceinline__ float group16_sum(float v) {
+    v += __shfl_xor_sync(0xffffffffu, v, 1);
+    v += __shfl_xor_sync(0xffffffffu, v, 2);
+    v += __shfl_xor_sync(0xffffffffu, v, 4);
+    v += __shfl_xor_sync(0xffffffffu, v, 8);
+    return v;
+}
+// exp2(a - b) with the convention that an empty state (a == -inf) contributes nothing
+__device__ __forceinline__ float safe_exp2_diff(float a, float b) {
+    return a == -INFINITY ? 0.f : exp2f(a - b);
+}
+
+template <int D, int G>
+__global__ void __launch_bounds__(kDecThreads)
+attn_decode_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __restrict__ k_cache,
+                   const __nv_bfloat16* __restrict__ v_cache, const int* __restrict__ block_table,
+                   const int* __restrict__ seq_lens, __nv_bfloat16* __restrict__ out, float* __restrict__ ws_o,
+                   float* __restrict__ ws_ml, int Hq, int Hkv, int block_size, int max_blocks, int num_splits,
+                   float scale_log2) {
+    constexpr int DL = D / 16;  // dims per lane
+    __shared__ float sm_m[kDecWarps][G];
+    __shared__ float sm_l[kDecWarps][G];
+    __shared__ float sm_acc[kDecWarps][G][D];
+
+    pdl_wait();
+    const int g = blockIdx.x, b = blockIdx.y, sp = blockIdx.z;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int grp = lane >> 4, sub = lane & 15;
+    const int L = seq_lens[b];
+    int chunk = (L + num_splits - 1) / num_splits;
+    chunk = (chunk + kTokPerIter - 1) / kTokPerIter * kTokPerIter;
+    const int begin = sp * chunk;
+    const int end = min(L, begin + chunk);
+
+    float qf[G][DL];
+#pragma unroll
+    for (int j = 0; j < G; ++j) {
+        RowVec<DL> r;
+        r.load(q + (static_cast<long long>(b) * Hq + g * G + j) * D + sub * DL);
+        r.unpack(qf[j]);
+#pragma unroll
+        for (int d = 0; d < DL; ++d) qf[j][d] *= scale_log2;
+    }
+    float m[G], l[G], acc[G][DL];
+#pragma unroll
+    for (int j = 0; j < G; ++j) {
+        m[j] = -INFINITY;
+        l[j] = 0.f;
+#pragma unroll
+        for (int d = 0; d < DL; ++d) acc[j][d] = 0.f;
+    }
+
+    const int* bt = block_table + static_cast<long long>(b) * max_blocks;
+    const long long head_stride = static_cast<long long>(block_size) * D;  // elements per (block, head)
+    auto row_offset = [&](int tok) -> long long {
+        const int c = min(tok, end - 1);  // clamp: masked rows still read a valid address
+        const int page = __ldg(bt + c / block_size);
+        return (static_cast<long long>(page) * Hkv + g) * head_stride + static_cast<long long>(c % block_size) * D +
+               sub * DL;
+    };
+
+    // Loop bounds are warp-uniform (the shuffles below need all 32 lanes); rows past `end` are
+    // read from a clamped, valid address and masked to -inf.
+    int wbase = begin + warp * 4;
+    RowVec<DL> k0, k1, v0, v1;
+    if (wbase < end) {
+        const long long o0 = row_offset(wbase + grp * 2), o1 = row_offset(wbase + grp * 2 + 1);
+        k0.load(k_cache + o0);
+        k1.load(k_cache + o1);
+        v0.load(v_cache + o0);
+        v1.load(v_cache + o1);
+    }
+    for (; wbase < end; wbase += kTokPerIter) {
+        const int base = wbase + grp * 2;
+        RowVec<DL> nk0, nk1, nv0, nv1;
+        if (wbase + kTokPerIter < end) {
+            const long long o0 = row_offset(base + kTokPerIter), o1 = row_offset(base + kTokPerIter + 1);
+            nk0.load(k_cache + o0);
+            nk1.load(k_cache + o1);
+            nv0.load(v_cache + o0);
+            nv1.load(v_cache + o1);
+        }
+        const bool valid0 = base < end, valid1 = base + 1 < end;
+        float kf0[DL], kf1[DL];
+        k0.unpack(kf0);
+        k1.unpack(kf1);
+        float s0[G], s1[G];
+#pragma unroll
+        for (int j = 0; j < G; ++j) {
+            float a = 0.f, c = 0.f;
+#pragma unroll
+            for (int d = 0; d < DL; ++d) {
+                a = fmaf(qf[j][d], kf0[d], a);
+                c = fmaf(qf[j][d], kf1[d], c);
+            }
+            a = group16_sum(a);
+            c = group16_sum(c);
+            s0[j] = valid0 ? a : -INFINITY;
+            s1[j] = valid1 ? c : -INFINITY;
+        }
+        float vf0[DL], vf1[DL];
+        v0.unpack(vf0);
+        v1.unpack(vf1);
+#pragma unroll
+        for (int j = 0; j < G; ++j) {
+            const float mn = fmaxf(m[j], fmaxf(s0[j], s1[j]));
+            const float mref = mn == -INFINITY ? 0.f : mn;  // nothing seen yet: every factor below is 0
+            const float corr = exp2f(m[j] - mref);
+            const float p0 = exp2f(s0[j] - mref);
+            const float p1 = exp2f(s1[j] - mref);
+            m[j] = mn;
+            l[j] = l[j] * corr + p0 + p1;
+#pragma unroll
+            for (int d = 0; d < DL; ++d) acc[j][d] = fmaf(p1, vf1[d], fmaf(p0, vf0[d], acc[j][d] * corr));
+        }
+        k0 = nk0;
+        k1 = nk1;
+        v0 = nv0;
+        v1 = nv1;
+    }
+
+    // merge the two lane groups of the warp
+#pragma unroll
+    for (int j = 0; j < G; ++j) {
+        const float mo = __shfl_xor_sync(0xffffffffu, m[j], 16);
+        const float lo = __shfl_xor_sync(0xffffffffu, l[j], 16);
+        const float mn = fmaxf(m[j], mo);
+        const float fs = safe_exp2_diff(m[j], mn), fo = safe_exp2_diff(mo, mn);
+        l[j] = l[j] * fs + lo * fo;
+#pragma unroll
+        for (int d = 0; d < DL; ++d) {
+            const float ao = __shfl_xor_sync(0xffffffffu, acc[j][d], 16);
+            acc[j][d] = acc[j][d] * fs + ao * fo;
+        }
+        m[j] = mn;
+    }
+    if (grp == 0) {
+#pragma unroll
+        for (int j = 0; j < G; ++j) {
+            if (sub == 0) {
+                sm_m[warp][j] = m[j];
+                sm_l[warp][j] = l[j];
+            }
+#pragma unroll
+            for (int d = 0; d < DL; ++d) sm_acc[warp][j][sub * DL + d] = acc[j][d];
+        }
+    }
+    __syncthreads();
+    pdl_launch_dependents();
+    // merge the warps; one (head, dim) item per thread-iteration
+    for (int it = threadIdx.x; it < G * D; it += kDecThreads) {
+        const int j = it / D, d = it % D;
+        float M = sm_m[0][j];
+#pragma unroll
+        for (int w = 1; w < kDecWarps; ++w) M = fmaxf(M, sm_m[w][j]);
+        float o = 0.f, ls = 0.f;
+#pragma unroll
+        for (int w = 0; w < kDecWarps; ++w) {
+            const float f = safe_exp2_diff(sm_m[w][j], M);
+            o += sm_acc[w][j][d] * f;
+            ls += sm_l[w][j] * f;
+        }
+        const long long h = static_cast<long long>(b) * Hq + g * G + j;
+        if (num_splits == 1) {
+            out[h * D + d] = __float2bfloat16_rn(ls > 0.f ? o / ls : 0.f);
+        } else {
+            ws_o[(h * num_splits + sp) * D + d] = o;
+            if (d == 0) {
+                ws_ml[(h * num_splits + sp) * 2] = M;
+                ws_ml[(h * num_splits + sp) * 2 + 1] = ls;
+            }
+        }
+    }
+}
+
+// out[h, :] = sum_s o_s * 2^(m_s - M) / sum_s l_s * 2^(m_s - M)
+__global__ void attn_decode_reduce_kernel(const float* __restrict__ ws_o, const float* __restrict__ ws_ml,
+                                          __nv_bfloat16* __restrict__ out, int D, int num_splits) {
+    pdl_wait();
+    const long long h = blockIdx.x;
+    const float* ml = ws_ml + h * num_splits * 2;
+    float M = -INFINITY;
+    for (int s = 0; s < num_splits; ++s) M = fmaxf(M, ml[2 * s]);
+    for (int d = threadIdx.x; d < D; d += blockDim.x) {
+        float o = 0.f, ls = 0.f;
+        for (int s = 0; s < num_splits; ++s) {
+            const float f = safe_exp2_diff(ml[2 * s], M);
+            o += ws_o[(h * num_splits + s) * D + d] * f;
+            ls += ml[2 * s + 1] * f;
+        }
+        out[h * D + d] = __float2bfloat16_rn(ls > 0.f ? o / ls : 0.f);
+    }
+    pdl_launch_dependents();
+}
+
+template <int D, int G>
+static int launch_decode(const void* q, const void* kc, const void* vc, const int* bt, const int* sl, void* out,
+                         float* ws_o, float* ws_ml, int B, int Hq, int Hkv, int block_size, int max_blocks,
+                         int num_splits, float scale, int flags, cudaStream_t stream) {
+    cudaLaunchConfig_t cfg = {};
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = (flags & ATX_FLAG_PDL) ? 1 : 0;
+    cfg.gridDim = dim3(static_cast<unsigned>(Hkv), static_cast<unsigned>(B), static_cast<unsigned>(num_splits));
+    cfg.blockDim = dim3(kDecThreads);
+    cfg.stream = stream;
+    ATX_CUDA(cudaLaunchKernelEx(&cfg, attn_decode_kernel<D, G>, reinterpret_cast<const __nv_bfloat16*>(q),
+                                reinterpret_cast<const __nv_bfloat16*>(kc), reinterpret_cast<const __nv_bfloat16*>(vc),
+                                bt, sl, reinterpret_cast<__nv_bfloat16*>(out), ws_o, ws_ml, Hq, Hkv, block_size,
+                                max_blocks, num_splits, scale * 1.4426950408889634f));
+    if (num_splits > 1) {
+        cfg.gridDim = dim3(static_cast<unsigned>(B * Hq));
+        cfg.blockDim = dim3(static_cast<unsigned>(D));
+        ATX_CUDA(cudaLaunchKernelEx(&cfg, attn_decode_reduce_kernel, static_cast<const float*>(ws_o),
+                                    static_cast<const float*>(ws_ml), reinterpret_cast<__nv_bfloat16*>(out), D,
+                                    num_splits));
+    }
+    return ATX_OK;
+}
+
+}  // namespace atx
+
+using namespace atx;
+
+extern "C" {
+
+long long atx_paged_attn_decode_workspace_bytes(int B, int Hq, int D, int num_splits) {
+    if (num_splits <= 1) return 0;
+    return static_cast<long long>(B) * Hq * num_splits * (D + 2) * 4;
+}
+
+int atx_paged_attn_decode(const void* q, const void* kc, const void* vc, const int* bt, const int* sl,
+                          void* out, void* workspace, long long workspace_bytes, int B, int Hq, int Hkv, int D,
+                          int block_size, int max_blocks, int num_splits, float scale, int flags,
+                          atx_stream_t stream_) {
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    ATX_REQUIRE(q && kc && vc && bt && sl && out, "atx_paged_attn_decode: null pointer");
+    ATX_REQUIRE(B > 0 && Hq > 0 && Hkv > 0 && Hq % Hkv == 0 && block_size > 0 && max_blocks > 0 && num_splits > 0,
+                "atx_paged_attn_decode: bad shape B=%d Hq=%d Hkv=%d block_size=%d max_blocks=%d splits=%d", B, Hq,
+                Hkv, block_size, max_blocks, num_splits);
+    ATX_REQUIRE(num_splits <= 65535 && B <= 65535, "atx_paged_attn_decode: B and num_splits must be <= 65535");
+    float* ws_o = nullptr;
+    float* ws_ml = nullptr;
+    if (num_splits > 1) {
+        const long long need = atx_paged_attn_decode_workspace_bytes(B, Hq, D, num_splits);
+        ATX_REQUIRE(workspace && workspace_bytes >= need,
+                    "atx_paged_attn_decode: workspace of %lld bytes needed, %lld given", need, workspace_bytes);
+        ws_o = static_cast<float*>(workspace);
+        ws_ml = ws_o + static_cast<long long>(B) * Hq * num_splits * D;
+    }
+    const int G = Hq / Hkv;
+#define ATX_DEC_CASE(DD, GG)                                                                                   \
+    if (D == DD && G == GG)                                                                                    \
+        return launch_decode<DD, GG>(q, kc, vc, bt, sl, out, ws_o, ws_ml, B, Hq, Hkv, block_size, max_blocks, \
+                                     num_splits, scale, flags, stream);
+    ATX_DEC_CASE(128, 4)
+    ATX_DEC_CASE(128, 8)
+    ATX_DEC_CASE(64, 4)
+    ATX_DEC_CASE(128, 1)
+    ATX_DEC_CASE(128, 2)
+    ATX_DEC_CASE(64, 1)
+    ATX_DEC_CASE(64, 2)
+    ATX_DEC_CASE(64, 8)
+#undef ATX_DEC_CASE
+    set_error("atx_paged_attn_decode: unsupported head_dim=%d / group=%d (head_dim 64|128, group 1|2|4|8)", D, G);
+    return ATX_ERR_UNSUPPORTED;
+}
+
+}  // extern "C"

@@ -1,0 +1,334 @@
+// bf16 projection / MLP / LM-head GEMM on tcgen05 tensor cores with TMEM accumulators.
+//
+//   out[t, n] (+)= sum_k X[t, k] * W[n, k]          X: [T, K] bf16 activations, W: [N, K] bf16
+//
+// This is torch.nn.functional.linear(x, W) as used by the reference's HF path
+// (transformers/models/llama/modeling_llama.py:182-184 MLP, :259-289 q/k/v/o, :499 lm_head) and by
+// vLLM's LlamaForCausalLM behind llm/serve_llm.py:527.
+//
+// B200 mapping ("swap-AB"): the WEIGHT matrix is the UMMA A operand (M = 128 output features per
+// CTA, one TMEM lane each) and the TOKENS are the UMMA B operand (N = TN tokens, TN in 16..256).
+// Decode batches (T = 1..32) therefore waste no tensor rows, and the kernel is what decode needs it
+// to be: a TMA-fed weight streamer. Both operands are K-major, staged by TMA into 128B-swizzled
+// shared memory through a kStages-deep mbarrier ring; one elected thread issues tcgen05.mma; the
+// fp32 accumulator tile [128 x TN] lives in TMEM and is read back with tcgen05.ld for the epilogue.
+// Split-K partial sums are combined with fp32 red.global.add straight into the destination, which
+// for o_proj / down_proj IS the fp32 residual stream (residual add fused, no workspace).
+#include "common.cuh"
+
+#include <mutex>
+#include <new>
+
+#include "../../include/atx_b200.h"
+
+namespace atx {
+
+constexpr int kBM = 128;  // weight rows per CTA (UMMA M)
+constexpr int kBK = 64;   // K elements per stage (= one 128-byte swizzle row of bf16)
+constexpr int kUK = 16;   // UMMA K for 16-bit inputs
+constexpr int kGemmThreads = 128;
+
+template <int TN>
+struct GemmCfg {
+    static constexpr int kStageBytesW = kBM * kBK * 2;  // 16 KB
+    static constexpr int kStageBytesX = TN * kBK * 2;
+    static constexpr int kStageBytes = kStageBytesW + kStageBytesX;
+    // decode tiles stay small enough for several CTAs per SM; prefill tiles take most of the SM
+    static constexpr int kStages = TN <= 32 ? 5 : (TN <= 64 ? 6 : (TN <= 128 ? 6 : 4));
+    static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+    static constexpr uint32_t kTmemCols = TN < 32 ? 32 : TN;
+};
+
+template <int TN>
+__global__ void __launch_bounds__(kGemmThreads)
+gemm_wt_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmX,
+               void* __restrict__ out, long long ldo, int T, int N, int kb_total, int kb_per_split,
+               int mode, int w_evict_first) {
+    using Cfg = GemmCfg<TN>;
+    extern __shared__ uint8_t smem_raw[];
+    // SWIZZLE_128B tiles must sit on 1024-byte boundaries
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                               ~static_cast<uintptr_t>(1023));
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
+    uint64_t* empty_bar = full_bar + Cfg::kStages;
+    uint64_t* accum_bar = empty_bar + Cfg::kStages;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_bar + 1);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int n0 = blockIdx.x * kBM;
+    const int t0 = blockIdx.y * TN;
+    const int kb_begin = blockIdx.z * kb_per_split;
+    const int kb_end = min(kb_total, kb_begin + kb_per_split);
+    const int nkb = kb_end - kb_begin;
+
+    if (warp == 0 && elect_one()) {
+        tma_prefetch_desc(&tmW);
+        tma_prefetch_desc(&tmX);
+#pragma unroll
+        for (int s = 0; s < Cfg::kStages; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        mbar_init(accum_bar, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_acc = *tmem_slot;
+
+    if (nkb > 0) {
+        if (warp == 0) {
+            if (elect_one()) {
+                // ===== TMA producer. Weights never depend on the previous kernel, so with
+                // programmatic dependent launch the first weight stages are already in flight
+                // while the producer of X is still finishing; only X waits for it.
+                const uint64_t polW = w_evict_first ? kEvictFirst : kEvictNormal;
+                const int pre = min(nkb, Cfg::kStages);
+                for (int i = 0; i < pre; ++i) {
+                    mbar_expect_tx(&full_bar[i], Cfg::kStageBytes);
+                    tma_load_2d(smem + i * Cfg::kStageBytes, &tmW, &full_bar[i],
+                                (kb_begin + i) * kBK, n0, polW);
+                }
+                pdl_wait();
+                for (int i = 0; i < pre; ++i) {
+                    tma_load_2d(smem + i * Cfg::kStageBytes + Cfg::kStageBytesW, &tmX, &full_bar[i],
+                                (kb_begin + i) * kBK, t0, kEvictLast);
+                }
+                int stage = 0;
+                uint32_t phase = 0;
+                for (int i = pre; i < nkb; ++i) {
+                    mbar_wait(&empty_bar[stage], phase);
+                    uint8_t* st = smem + stage * Cfg::kStageBytes;
+                    mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+                    tma_load_2d(st, &tmW, &full_bar[stage], (kb_begin + i) * kBK, n0, polW);
+                    tma_load_2d(st + Cfg::kStageBytesW, &tmX, &full_bar[stage], (kb_begin + i) * kBK,
+                                t0, kEvictLast);
+                    if (++stage == Cfg::kStages) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                }
+            }
+        } else if (warp == 1) {
+            if (elect_one()) {
+                // ===== MMA issuer (single thread)
+                constexpr uint32_t idesc = umma_idesc_bf16(kBM, TN);
+                int stage = 0;
+                uint32_t phase = 0;
+                for (int i = 0; i < nkb; ++i) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tc_fence_after();
+                    const uint32_t a_addr = smem_u32(smem + stage * Cfg::kStageBytes);
+                    const uint32_t b_addr = a_addr + Cfg::kStageBytesW;
+                    const uint64_t a_desc = umma_desc_sw128(a_addr);
+                    const uint64_t b_desc = umma_desc_sw128(b_addr);
+#pragma unroll
+                    for (int k = 0; k < kBK / kUK; ++k) {
+                        // advance 16 elements (32 B) along K inside the swizzle row: +2 in the
+                        // 16-byte-granular start-address field
+                        umma_bf16(tmem_acc, a_desc + 2 * k, b_desc + 2 * k, idesc,
+                                  (i > 0 || k > 0) ? 1u : 0u);
+                    }
+                    umma_commit(&empty_bar[stage]);  // frees the smem slot when the MMAs retire
+                    if (++stage == Cfg::kStages) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                }
+                umma_commit(accum_bar);  // accumulator complete
+            }
+        }
+        __syncwarp();
+
+        // ===== epilogue: all four warps; warp w owns TMEM lanes [32w, 32w+32) = weight rows
+        mbar_wait(accum_bar, 0);
+        tc_fence_after();
+        pdl_launch_dependents();
+        const int n = n0 + warp * 32 + lane;
+        const bool n_ok = n < N;
+#pragma unroll 1
+        for (int c = 0; c < TN; c += 16) {
+            if (t0 + c >= T) break;  // warp-uniform
+            uint32_t v[16];
+            tmem_ld16(tmem_acc + (static_cast<uint32_t>(warp * 32) << 16) + c, v);
+            tmem_ld_wait();
+            if (n_ok) {
+                if (mode == ATX_GEMM_STORE_F32) {
+                    float* o = reinterpret_cast<float*>(out);
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        const int t = t0 + c + j;
+                        if (t < T) o[static_cast<long long>(t) * ldo + n] = __uint_as_float(v[j]);
+                    }
+                } else if (mode == ATX_GEMM_ADD_F32) {
+                    float* o = reinterpret_cast<float*>(out);
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        const int t = t0 + c + j;
+                        if (t < T) atomicAdd(o + static_cast<long long>(t) * ldo + n, __uint_as_float(v[j]));
+                    }
+                } else {
+                    __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out);
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        const int t = t0 + c + j;
+                        if (t < T)
+                            o[static_cast<long long>(t) * ldo + n] = __float2bfloat16_rn(__uint_as_float(v[j]));
+                    }
+                }
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc<Cfg::kTmemCols>(tmem_acc);
+}
+
+// ---- host side ---------------------------------------------------------------------------------------
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    });
+    return fn;
+}
+
+// rows x cols bf16 row-major (row stride ld elements), box = box_rows x 64 columns, 128B swizzle
+static int make_map(CUtensorMap* m, const void* base, long long rows, long long cols, long long ld,
+                    int box_rows) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) {
+        set_error("cuTensorMapEncodeTiled not available from the driver");
+        return ATX_ERR_CUDA;
+    }
+    cuuint64_t dims[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
+    cuuint64_t strides[1] = {static_cast<cuuint64_t>(ld) * 2};
+    cuuint32_t box[2] = {static_cast<cuuint32_t>(kBK), static_cast<cuuint32_t>(box_rows)};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box,
+                    estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled failed (CUresult %d) rows=%lld cols=%lld ld=%lld box_rows=%d",
+                  static_cast<int>(r), rows, cols, ld, box_rows);
+        return ATX_ERR_CUDA;
+    }
+    return ATX_OK;
+}
+
+static const int kTileSizes[5] = {16, 32, 64, 128, 256};
+
+}  // namespace atx
+
+struct atx_gemm_plan {
+    CUtensorMap tmW;
+    CUtensorMap tmX[5];  // one per token-tile size
+    long long N, K, T_cap;
+    int w_evict_first;
+};
+
+using namespace atx;
+
+template <int TN>
+static int launch_gemm(const atx_gemm_plan* p, int ti, void* out, long long ldo, int T, int mode,
+                       int splits, int pdl, cudaStream_t stream) {
+    using Cfg = GemmCfg<TN>;
+    static bool attr_done = false;  // per-instantiation; benign race (idempotent call)
+    if (!attr_done) {
+        ATX_CUDA(cudaFuncSetAttribute(gemm_wt_kernel<TN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      Cfg::kSmemBytes));
+        attr_done = true;
+    }
+    const int kb_total = static_cast<int>(p->K / kBK);
+    const int kb_per = (kb_total + splits - 1) / splits;
+    const int zs = (kb_total + kb_per - 1) / kb_per;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(static_cast<unsigned>((p->N + kBM - 1) / kBM), static_cast<unsigned>((T + TN - 1) / TN),
+                       static_cast<unsigned>(zs));
+    cfg.blockDim = dim3(kGemmThreads);
+    cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    ATX_CUDA(cudaLaunchKernelEx(&cfg, gemm_wt_kernel<TN>, p->tmW, p->tmX[ti], out, ldo, T,
+                                static_cast<int>(p->N), kb_total, kb_per, mode, p->w_evict_first));
+    return ATX_OK;
+}
+
+extern "C" {
+
+int atx_gemm_plan_create(atx_gemm_plan** plan, const void* W, long long N, long long K, const void* X,
+                         long long T_cap, long long ldx) {
+    ATX_REQUIRE(plan && W && X, "atx_gemm_plan_create: null pointer");
+    ATX_REQUIRE(N > 0 && K > 0 && T_cap > 0 && ldx >= K, "atx_gemm_plan_create: bad shape N=%lld K=%lld T_cap=%lld ldx=%lld", N, K, T_cap, ldx);
+    ATX_REQUIRE(K % kBK == 0, "atx_gemm_plan_create: K=%lld must be a multiple of %d", K, kBK);
+    ATX_REQUIRE((reinterpret_cast<uintptr_t>(W) & 15) == 0 && (reinterpret_cast<uintptr_t>(X) & 15) == 0 &&
+                    (ldx * 2) % 16 == 0,
+                "atx_gemm_plan_create: W, X and the X row pitch must be 16-byte aligned");
+    atx_gemm_plan* p = new (std::nothrow) atx_gemm_plan();
+    ATX_REQUIRE(p != nullptr, "atx_gemm_plan_create: out of host memory");
+    p->N = N;
+    p->K = K;
+    p->T_cap = T_cap;
+    // weights larger than L2 are streamed once per step: do not let them evict activations / KV
+    p->w_evict_first = (N * K * 2 > (64ll << 20)) ? 1 : 0;
+    int rc = make_map(&p->tmW, W, N, K, K, kBM);
+    for (int i = 0; i < 5 && rc == ATX_OK; ++i) rc = make_map(&p->tmX[i], X, T_cap, K, ldx, kTileSizes[i]);
+    if (rc != ATX_OK) {
+        delete p;
+        return rc;
+    }
+    *plan = p;
+    return ATX_OK;
+}
+
+void atx_gemm_plan_destroy(atx_gemm_plan* plan) { delete plan; }
+
+int atx_gemm_auto_splits(long long N, long long K, int T) {
+    // Decode-sized batches are pure weight streaming: cut K until roughly two CTAs per SM are
+    // resident so that every SM has TMA loads in flight, but keep >= 8 k-blocks (128 KB) per CTA.
+    if (T > 64) return 1;
+    const long long tiles = (N + kBM - 1) / kBM;
+    const int kb = static_cast<int>(K / kBK);
+    const int target = 2 * num_sms();
+    int s = 1;
+    while (tiles * s < target && kb / (s * 2) >= 8) s *= 2;
+    return s;
+}
+
+int atx_gemm_run(const atx_gemm_plan* p, void* out, long long ldo, int T, int mode, int splits, int flags,
+                 atx_stream_t stream_) {
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    ATX_REQUIRE(p && out, "atx_gemm_run: null pointer");
+    ATX_REQUIRE(T > 0 && T <= p->T_cap, "atx_gemm_run: T=%d outside (0, %lld]", T, p->T_cap);
+    ATX_REQUIRE(mode >= ATX_GEMM_STORE_F32 && mode <= ATX_GEMM_STORE_BF16, "atx_gemm_run: bad mode %d", mode);
+    ATX_REQUIRE(ldo >= p->N, "atx_gemm_run: ldo=%lld < N=%lld", ldo, p->N);
+    if (splits <= 0) splits = (mode == ATX_GEMM_ADD_F32) ? atx_gemm_auto_splits(p->N, p->K, T) : 1;
+    ATX_REQUIRE(splits == 1 || mode == ATX_GEMM_ADD_F32,
+                "atx_gemm_run: split-K (%d) needs ATX_GEMM_ADD_F32 into a zeroed or residual buffer", splits);
+    const int pdl = (flags & ATX_FLAG_PDL) ? 1 : 0;
+    if (T <= 16) return launch_gemm<16>(p, 0, out, ldo, T, mode, splits, pdl, stream);
+    if (T <= 32) return launch_gemm<32>(p, 1, out, ldo, T, mode, splits, pdl, stream);
+    if (T <= 64) return launch_gemm<64>(p, 2, out, ldo, T, mode, splits, pdl, stream);
+    if (T <= 128) return launch_gemm<128>(p, 3, out, ldo, T, mode, splits, pdl, stream);
+    return launch_gemm<256>(p, 4, out, ldo, T, mode, splits, pdl, stream);
+}
+
+}  // extern "C"

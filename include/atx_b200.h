@@ -1,0 +1,121 @@
+/* atx_b200 — C ABI of the B200-native Llama inference kernels (libatx_b200.so).
+ *
+ * The reference (dlamagna/agentic-traffic-testing) has no FFI of its own: its L5 llm-backend calls
+ * the third-party engines vLLM (llm/serve_llm.py:374-379, 521-531) and HF transformers
+ * (llm/hf_cpu_server.py:39-50, 91). This header is the seam a replacement engine binds beneath
+ * `AsyncVLLMBackend.generate` (llm/serve_llm.py:504): each entry point names the reference
+ * arithmetic it replaces. All pointers are DEVICE pointers unless stated; every buffer is owned by
+ * the caller; calls are asynchronous on `stream`, never synchronise the host and (unless stated)
+ * allocate nothing. Return value: 0 on success, negative on error with text in atx_last_error().
+ *
+ * Numeric conventions: activations entering a GEMM are bf16, the residual stream and GEMM
+ * accumulators are fp32, the KV cache is bf16, softmax / norms reduce in fp32.
+ * Index conventions: token ids, positions, slots, block tables and lengths are int32.
+ */
+#ifndef ATX_B200_H
+#define ATX_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* atx_stream_t; /* a cudaStream_t */
+
+#define ATX_VERSION 100
+
+/* error codes */
+#define ATX_OK 0
+#define ATX_ERR_ARG -1
+#define ATX_ERR_CUDA -2
+#define ATX_ERR_UNSUPPORTED -3
+#define ATX_ERR_LIMIT -4
+
+/* flags */
+#define ATX_FLAG_PDL 1 /* launch with programmatic dependent launch (stream serialization) */
+
+/* Thread-local text of the last error raised on the calling thread. Never NULL. */
+const char* atx_last_error(void);
+int atx_version(void);
+/* Device facts of the current device (host pointers may be NULL). */
+int atx_device_info(int* sm_count, int* cc_major, int* cc_minor);
+
+/* ---- GEMM: out[t, n] (+)= sum_k X[t, k] * W[n, k] -------------------------------------------------
+ * Replaces torch.nn.functional.linear in transformers/models/llama/modeling_llama.py:182-184
+ * (gate/up/down), :259-289 (q/k/v/o) and :499 (lm_head). W: [N, K] bf16 row-major (HF layout),
+ * X: [T_cap, ldx] bf16. A plan caches the TMA descriptors for one (W, X buffer) pair; creating it
+ * is host-only work (no device allocation, no launch). T may vary per call (1..T_cap). */
+typedef struct atx_gemm_plan atx_gemm_plan;
+#define ATX_GEMM_STORE_F32 0  /* out fp32 = acc                                            */
+#define ATX_GEMM_ADD_F32 1    /* out fp32 += acc (atomic; enables split-K; fuses residual) */
+#define ATX_GEMM_STORE_BF16 2 /* out bf16 = round(acc)                                     */
+int atx_gemm_plan_create(atx_gemm_plan** plan, const void* W, long long N, long long K, const void* X,
+                         long long T_cap, long long ldx);
+void atx_gemm_plan_destroy(atx_gemm_plan* plan);
+/* splits: K partitions (>=1); 0 = choose (only ADD mode may split). ldo: out row pitch in elements. */
+int atx_gemm_run(const atx_gemm_plan* plan, void* out, long long ldo, int T, int mode, int splits,
+                 int flags, atx_stream_t stream);
+int atx_gemm_auto_splits(long long N, long long K, int T);
+
+/* ---- embedding gather: out[t, :] = float(table[ids[t], :]) ---------------------------------------
+ * Replaces LlamaModel.embed_tokens (modeling_llama.py:375-427). table: [V, H] bf16, out fp32. */
+int atx_embed_gather(const int* ids, const void* table, float* out, int T, int H, int V,
+                     atx_stream_t stream);
+
+/* ---- RMSNorm: out[t, :] = bf16( w * x[r, :] * rsqrt(mean(x[r, :]^2) + eps) ), r = rows ? rows[t] : t
+ * Replaces LlamaRMSNorm.forward (modeling_llama.py:62-67). x fp32 (the residual stream), w bf16,
+ * out bf16. Optionally zero-fills `zero_ptr[0 .. zero_bytes)` (16-byte multiple) for a following
+ * split-K GEMM, saving a memset node. */
+int atx_rmsnorm(const float* x, const int* rows, const void* w, void* out, int T, int H, float eps,
+                void* zero_ptr, long long zero_bytes, int flags, atx_stream_t stream);
+
+/* ---- RoPE + KV-cache write ------------------------------------------------------------------------
+ * Replaces apply_rotary_pos_emb (modeling_llama.py:146-168, rotate_half layout :138-143) and
+ * past_key_values.update (:267) / vLLM reshape_and_cache. qkv: [T, (Hq + 2*Hkv) * D] fp32 (GEMM
+ * output), cos_sin: [max_pos, D] fp32 (row p = cos(p*inv_freq[0..D/2)) ++ sin(...)), positions[T],
+ * slots[T] (slot = block * block_size + offset; negative = skip the cache write).
+ * q_out: [T, Hq * D] bf16. K and V caches: [num_blocks, Hkv, block_size, D] bf16 each. */
+int atx_rope_kv_write(const float* qkv, const int* positions, const int* slots, const float* cos_sin,
+                      void* q_out, void* k_cache, void* v_cache, int T, int Hq, int Hkv, int D,
+                      int block_size, int flags, atx_stream_t stream);
+
+/* ---- SwiGLU: act[t, i] = bf16( silu(gu[t, i]) * gu[t, I + i] ) ------------------------------------
+ * Replaces LlamaMLP.forward's act_fn(gate) * up (modeling_llama.py:182-184). gu: [T, 2*I] fp32. */
+int atx_silu_mul(const float* gu, void* act, int T, int I, int flags, atx_stream_t stream);
+
+/* ---- paged attention, decode (one query token per sequence) ---------------------------------------
+ * Replaces eager_attention_forward (modeling_llama.py:199-222; repeat_kv :187-196; fp32 softmax
+ * :217) over vLLM's paged KV (FlashInfer decode). q: [B, Hq * D] bf16; out: [B, Hq * D] bf16;
+ * block_table: [B, max_blocks] int32; seq_lens[B] = tokens in cache INCLUDING the current one.
+ * workspace: fp32 scratch of atx_paged_attn_decode_workspace_bytes(B, Hq, D, num_splits) bytes,
+ * supplied by the caller (partial outputs + running max / sum per split). */
+long long atx_paged_attn_decode_workspace_bytes(int B, int Hq, int D, int num_splits);
+int atx_paged_attn_decode(const void* q, const void* k_cache, const void* v_cache, const int* block_table,
+                          const int* seq_lens, void* out, void* workspace, long long workspace_bytes,
+                          int B, int Hq, int Hkv, int D, int block_size, int max_blocks, int num_splits,
+                          float scale, int flags, atx_stream_t stream);
+
+/* ---- paged attention, prefill / chunked prefill (causal) ------------------------------------------
+ * Same arithmetic as above with the causal mask of create_causal_mask; queries of sequence s are
+ * rows [cu_q[s], cu_q[s+1]) of q, and their keys are the first ctx_lens[s] cache tokens of that
+ * sequence (the chunk's own K/V must already be in the cache): query j of n attends to keys
+ * [0, ctx_lens[s] - n + j]. q/out: [T, Hq * D] bf16. */
+int atx_paged_attn_prefill(const void* q, const void* k_cache, const void* v_cache, const int* block_table,
+                           const int* cu_q, const int* ctx_lens, void* out, int S, int max_q_len, int Hq,
+                           int Hkv, int D, int block_size, int max_blocks, float scale, int flags,
+                           atx_stream_t stream);
+
+/* ---- sampler --------------------------------------------------------------------------------------
+ * Replaces vLLM SamplingParams(temperature=0.2) (llm/serve_llm.py:379, 521) / HF do_sample
+ * (llm/hf_cpu_server.py:91) and greedy arg-max used for parity. logits: [B, ldl] fp32, V valid.
+ * temperature[b] <= 0 => arg-max (lowest index wins ties, as torch.argmax). Otherwise an exact
+ * categorical draw from softmax(logits / temperature) restricted to the top-p nucleus, by the
+ * Gumbel-max rule with the counter-based generator documented in oracle/sampler_ref.py
+ * (seeds[b], steps[b] select the stream). out_ids: [B] int32. */
+int atx_sample(const float* logits, long long ldl, const float* temperature, const float* top_p,
+               const unsigned long long* seeds, const int* steps, int* out_ids, int B, int V, int flags,
+               atx_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ATX_B200_H */

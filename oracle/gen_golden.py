@@ -1,0 +1,90 @@
+"""Mint golden vectors from the reference's own CPU arithmetic (run in the BUILD container only).
+
+`llm/hf_cpu_server.py:39-50` loads `transformers.AutoModelForCausalLM` (= LlamaForCausalLM for the
+Llama checkpoints it names) in fp32 on CPU; this script instantiates that class from a LlamaConfig,
+loads the seeded weights of oracle.llama_ref.init_weights, and records what it computes. The
+fixtures land in tests/golden/ and are committed; tests never need transformers' weights or network.
+
+    python -m oracle.gen_golden            # writes tests/golden/hf_<shape>.npz
+"""
+from __future__ import annotations
+
+import sys
+from pathlib import Path
+
+import numpy as np
+import torch
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+
+from oracle.llama_ref import LlamaShape, RefLlama, init_weights, shape_by_name  # noqa: E402
+
+
+def hf_model(shape: LlamaShape, weights):
+    from transformers import LlamaConfig, LlamaForCausalLM
+
+    cfg = LlamaConfig(
+        vocab_size=shape.vocab_size, hidden_size=shape.hidden_size, intermediate_size=shape.intermediate_size,
+        num_hidden_layers=shape.num_hidden_layers, num_attention_heads=shape.num_attention_heads,
+        num_key_value_heads=shape.num_key_value_heads, head_dim=shape.head_dim, rms_norm_eps=shape.rms_norm_eps,
+        rope_theta=shape.rope_theta, rope_scaling=dict(shape.rope_scaling) if shape.rope_scaling else None,
+        tie_word_embeddings=shape.tie_word_embeddings, max_position_embeddings=shape.max_position_embeddings,
+        attention_bias=False, mlp_bias=False, hidden_act="silu", attn_implementation="eager",
+    )
+    with torch.device("meta"):
+        model = LlamaForCausalLM(cfg)
+    model = model.to_empty(device="cpu").to(torch.float32)
+    sd = {k: v.clone() for k, v in weights.items()}
+    if shape.tie_word_embeddings:
+        sd["lm_head.weight"] = sd["model.embed_tokens.weight"]
+    missing, unexpected = model.load_state_dict(sd, strict=False)
+    assert not unexpected, unexpected
+    assert all("rotary" in m or "inv_freq" in m for m in missing), missing
+    # buffers (inv_freq) were created on meta: rebuild the rotary embedding on CPU
+    from transformers.models.llama.modeling_llama import LlamaRotaryEmbedding
+
+    model.model.rotary_emb = LlamaRotaryEmbedding(config=cfg, device="cpu")
+    model.eval()
+    return model
+
+
+def make(shape_name: str, seed: int, prompt_seed: int, prompt_len: int, new_tokens: int, out: Path) -> None:
+    shape = shape_by_name(shape_name)
+    weights = init_weights(shape, seed)
+    model = hf_model(shape, weights)
+    g = torch.Generator().manual_seed(prompt_seed)
+    prompt = torch.randint(0, shape.vocab_size, (prompt_len,), generator=g)
+    with torch.no_grad():
+        res = model(prompt[None], output_hidden_states=True)
+        logits = res.logits[0]
+        gen = model.generate(prompt[None], max_new_tokens=new_tokens, min_new_tokens=new_tokens, do_sample=False,
+                             pad_token_id=0)
+        greedy = gen[0, prompt_len:]
+        # llama3 rope beyond the original context: positions around 8192 * factor boundary
+        far = torch.tensor([0, 1, 777, 8191, 8192, 20000, 131071])
+        cos, sin = model.model.rotary_emb(torch.zeros(1, 1, 1), far[None])
+    ref = RefLlama(shape, weights)
+    with torch.no_grad():
+        ref_logits = ref.forward(prompt)
+    err = (ref_logits - logits).abs().max().item()
+    print(f"{shape_name}: restatement vs HF max-abs logits err = {err:.3e}; greedy = {greedy[:8].tolist()}...")
+    assert err < 2e-4, err
+    np.savez_compressed(
+        out,
+        shape_name=np.array(shape_name), seed=np.array(seed), prompt=prompt.numpy().astype(np.int32),
+        logits_last=logits[-1].numpy(), logits_first=logits[0].numpy(),
+        hidden_last_layer=res.hidden_states[-1][0, -1].numpy(),  # after final norm (HF convention)
+        hidden_layer1=res.hidden_states[1][0].numpy(),
+        greedy=greedy.numpy().astype(np.int32),
+        inv_freq=model.model.rotary_emb.inv_freq.numpy(),
+        far_pos=far.numpy().astype(np.int32), far_cos=cos[0].numpy(), far_sin=sin[0].numpy(),
+    )
+    print(f"wrote {out} ({out.stat().st_size / 1024:.0f} KiB)")
+
+
+if __name__ == "__main__":
+    gold = ROOT / "tests" / "golden"
+    gold.mkdir(parents=True, exist_ok=True)
+    make("tiny", seed=11, prompt_seed=12, prompt_len=40, new_tokens=32, out=gold / "hf_tiny.npz")
+    make("tiny128", seed=21, prompt_seed=22, prompt_len=33, new_tokens=32, out=gold / "hf_tiny128.npz")

@@ -1,0 +1,325 @@
+"""Per-kernel parity: every C-ABI entry point against the CPU oracle on identical (bf16-rounded)
+inputs. Integer work (page scatter, arg-max) is bit-exact; floating point uses the tolerance
+stated beside each check."""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import llama_ref as R
+from oracle import sampler_ref as SR
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def cabi():
+    from atx import _cabi
+
+    _cabi.load()
+    return _cabi
+
+
+def _bf16(t):
+    return t.to(torch.bfloat16)
+
+
+# ---------------------------------------------------------------------------------------- GEMM
+GEMM_CASES = [
+    # T, N, K, mode, splits
+    (1, 128, 64, 0, 1),
+    (6, 256, 512, 0, 1),
+    (6, 384, 4096, 1, 4),
+    (16, 128, 128, 2, 1),
+    (17, 256, 1024, 0, 1),
+    (33, 512, 256, 1, 2),
+    (100, 256, 512, 2, 1),
+    (130, 384, 1024, 0, 1),
+    (300, 256, 2048, 1, 1),
+    (6, 200, 192, 0, 1),       # N not a multiple of 128: TMA zero fill + guarded stores
+    (6, 6144, 4096, 1, 0),     # 8B qkv shape, automatic split-K
+    (512, 1024, 4096, 2, 1),   # prefill-like tile (TN = 256, two token tiles)
+]
+
+
+@pytest.mark.parametrize("T,N,K,mode,splits", GEMM_CASES)
+def test_gemm_matches_fp32_reference(cabi, T, N, K, mode, splits):
+    g = torch.Generator().manual_seed(T * 131 + N * 7 + K)
+    x = _bf16(torch.randn(T, K, generator=g))
+    w = _bf16(torch.randn(N, K, generator=g) * 0.05)
+    ref = x.float() @ w.float().T  # exact products of bf16 values, fp32/64-safe reference
+    ref64 = (x.double() @ w.double().T)
+    t_cap = max(T, 8)
+    xb = torch.zeros(t_cap, K, dtype=torch.bfloat16, device="cuda")
+    xb[:T] = x.cuda()
+    plan = cabi.GemmPlan(w.cuda().contiguous(), xb)
+    if mode == 2:
+        out = torch.full((T, N), 7.0, dtype=torch.bfloat16, device="cuda")
+    elif mode == 1:
+        base = torch.randn(T, N, generator=g)
+        out = base.cuda().clone()
+    else:
+        out = torch.full((T, N), 7.0, dtype=torch.float32, device="cuda")
+    plan.run(out, T, mode, splits)
+    torch.cuda.synchronize()
+    got = out.float().cpu().double()
+    want = ref64 + (base.double() if mode == 1 else 0)
+    # fp32 accumulation over K terms of magnitude ~|x||w|: relative 1e-5 of the row scale + bf16 output rounding
+    scale = (x.double().abs() @ w.double().abs().T)
+    tol = 2e-6 * scale + (2 ** -8 * want.abs() if mode == 2 else 0) + 1e-6
+    assert torch.all((got - want).abs() <= tol), float(((got - want).abs() - tol).max())
+    assert ref.shape == got.shape
+
+
+def test_gemm_rows_beyond_T_do_not_leak(cabi):
+    """Rows of the X buffer past T (stale data, even NaN) must not influence rows < T."""
+    K, N, T = 256, 256, 5
+    g = torch.Generator().manual_seed(3)
+    xb = _bf16(torch.randn(16, K, generator=g)).cuda()
+    xb[T:] = float("nan")
+    w = _bf16(torch.randn(N, K, generator=g)).cuda()
+    out = torch.zeros(16, N, device="cuda")
+    cabi.GemmPlan(w, xb).run(out, T, 0)
+    torch.cuda.synchronize()
+    want = xb[:T].float().cpu() @ w.float().cpu().T
+    assert torch.allclose(out[:T].cpu(), want, rtol=1e-4, atol=1e-3)
+    assert torch.all(out[T:] == 0)
+
+
+def test_gemm_rejects_bad_arguments(cabi):
+    w = torch.zeros(128, 96, dtype=torch.bfloat16, device="cuda")
+    x = torch.zeros(8, 96, dtype=torch.bfloat16, device="cuda")
+    with pytest.raises(cabi.AtxError, match="multiple of 64"):
+        cabi.GemmPlan(w, x)
+    w = torch.zeros(128, 128, dtype=torch.bfloat16, device="cuda")
+    x = torch.zeros(8, 128, dtype=torch.bfloat16, device="cuda")
+    plan = cabi.GemmPlan(w, x)
+    out = torch.zeros(8, 128, device="cuda")
+    with pytest.raises(cabi.AtxError, match="outside"):
+        plan.run(torch.zeros(16, 128, device="cuda"), 9, 0)
+    with pytest.raises(cabi.AtxError, match="split-K"):
+        plan.run(out, 4, 0, splits=2)
+
+
+# ---------------------------------------------------------------------------------- pointwise
+def test_embed_gather_exact(cabi):
+    g = torch.Generator().manual_seed(5)
+    table = _bf16(torch.randn(1000, 512, generator=g))
+    ids = torch.randint(0, 1000, (37,), generator=g, dtype=torch.int32)
+    out = torch.empty(37, 512, device="cuda")
+    cabi.embed_gather(ids.cuda(), table.cuda(), out, 37)
+    assert torch.equal(out.cpu(), table.float()[ids.long()])
+
+
+@pytest.mark.parametrize("T,H", [(1, 512), (6, 4096), (33, 2048), (5, 8192)])
+def test_rmsnorm(cabi, T, H):
+    g = torch.Generator().manual_seed(T + H)
+    x = torch.randn(T, H, generator=g) * 3
+    w = _bf16(1 + 0.1 * torch.randn(H, generator=g))
+    out = torch.empty(T, H, dtype=torch.bfloat16, device="cuda")
+    zero = torch.full((1000, 4), 5.0, device="cuda")
+    cabi.rmsnorm(x.cuda(), w.cuda(), out, T, 1e-5, zero=zero)
+    want = R.rms_norm(x, w.float(), 1e-5)
+    # one bf16 rounding of an O(1) value computed in fp32
+    assert torch.all((out.float().cpu() - want).abs() <= 2 ** -8 * want.abs() + 1e-6)
+    assert torch.all(zero == 0)
+
+
+def test_rmsnorm_row_gather(cabi):
+    g = torch.Generator().manual_seed(9)
+    x = torch.randn(20, 512, generator=g)
+    w = _bf16(torch.ones(512))
+    rows = torch.tensor([19, 3, 7], dtype=torch.int32)
+    out = torch.empty(3, 512, dtype=torch.bfloat16, device="cuda")
+    cabi.rmsnorm(x.cuda(), w.cuda(), out, 3, 1e-5, rows=rows.cuda())
+    want = R.rms_norm(x[rows.long()], w.float(), 1e-5)
+    assert torch.all((out.float().cpu() - want).abs() <= 2 ** -8 * want.abs() + 1e-6)
+
+
+@pytest.mark.parametrize("shape_name", ["tiny", "8b"])
+def test_rope_kv_write_bit_exact(cabi, shape_name):
+    """q (bf16) and the K/V pages must equal the oracle's rope + bf16 rounding exactly, and the
+    scatter must hit exactly the slots of the block table (integer indexing: bit-exact)."""
+    s = R.shape_by_name(shape_name)
+    Hq, Hkv, D, bs = s.num_attention_heads, s.num_key_value_heads, s.head_dim, 16
+    T, nblocks = 23, 12
+    g = torch.Generator().manual_seed(17)
+    qkv = torch.randn(T, (Hq + 2 * Hkv) * D, generator=g)
+    positions = torch.tensor([0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 100, 101, 102, 8191, 8192, 8193, 20000, 20001, 30000,
+                              30001, 30002, 32767, 5], dtype=torch.int32)
+    table = [7, 2, 9]
+    slots = torch.tensor(R.slot_mapping(table, 10, T - 1, bs) + [-1], dtype=torch.int32)
+    cs = R.cos_sin_table(s, 32768)
+    kc = torch.zeros(nblocks, Hkv, bs, D, dtype=torch.bfloat16, device="cuda")
+    vc = torch.zeros_like(kc)
+    qo = torch.empty(T, Hq * D, dtype=torch.bfloat16, device="cuda")
+    cabi.rope_kv_write(qkv.cuda(), positions.cuda(), slots.cuda(), cs.cuda(), qo, kc, vc, T, Hq, Hkv, D, bs)
+    cos, sin = R.rope_cos_sin(positions, R.llama3_inv_freq(s))
+    q = qkv[:, : Hq * D].view(T, Hq, D)
+    k = qkv[:, Hq * D: (Hq + Hkv) * D].view(T, Hkv, D)
+    v = qkv[:, (Hq + Hkv) * D:].view(T, Hkv, D)
+    q_ref = R.apply_rope(q, cos, sin).to(torch.bfloat16)
+    k_ref = R.apply_rope(k, cos, sin).to(torch.bfloat16)
+    assert torch.equal(qo.cpu().view(T, Hq, D), q_ref)
+    kc_ref = torch.zeros(nblocks, Hkv, bs, D, dtype=torch.bfloat16)
+    vc_ref = torch.zeros_like(kc_ref)
+    for t in range(T):
+        sl = int(slots[t])
+        if sl < 0:
+            continue
+        kc_ref[sl // bs, :, sl % bs] = k_ref[t]
+        vc_ref[sl // bs, :, sl % bs] = v[t].to(torch.bfloat16)
+    assert torch.equal(kc.cpu(), kc_ref)
+    assert torch.equal(vc.cpu(), vc_ref)
+
+
+def test_silu_mul(cabi):
+    g = torch.Generator().manual_seed(23)
+    T, I = 7, 1024
+    gu = torch.randn(T, 2 * I, generator=g) * 4
+    act = torch.empty(T, I, dtype=torch.bfloat16, device="cuda")
+    cabi.silu_mul(gu.cuda(), act, T, I)
+    want = R.swiglu(gu[:, :I], gu[:, I:])
+    assert torch.all((act.float().cpu() - want).abs() <= 2 ** -8 * want.abs() + 1e-6)
+
+
+# ---------------------------------------------------------------------------------- attention
+def _paged_case(seed, lens, Hq, Hkv, D, bs=16, extra_blocks=5):
+    """Random K/V for every sequence scattered into shuffled pages (+ NaN in unused rows)."""
+    g = torch.Generator().manual_seed(seed)
+    need = [(L + bs - 1) // bs for L in lens]
+    nblocks = sum(need) + extra_blocks
+    perm = torch.randperm(nblocks, generator=g).tolist()
+    kc = torch.full((nblocks, Hkv, bs, D), float("nan"), dtype=torch.bfloat16)
+    vc = torch.full_like(kc, float("nan"))
+    tables, ks, vs = [], [], []
+    max_blocks = max(need) + 2
+    for i, L in enumerate(lens):
+        tbl = [perm.pop() for _ in range(need[i])]
+        k = _bf16(torch.randn(L, Hkv, D, generator=g))
+        v = _bf16(torch.randn(L, Hkv, D, generator=g))
+        for p in range(L):
+            kc[tbl[p // bs], :, p % bs] = k[p]
+            vc[tbl[p // bs], :, p % bs] = v[p]
+        tables.append(tbl + [0] * (max_blocks - len(tbl)))
+        ks.append(k.float())
+        vs.append(v.float())
+    return kc, vc, torch.tensor(tables, dtype=torch.int32), ks, vs
+
+
+@pytest.mark.parametrize("Hq,Hkv,D", [(32, 8, 128), (8, 2, 64), (8, 1, 128), (4, 4, 64)])
+@pytest.mark.parametrize("splits", [1, 3, 8])
+def test_paged_decode_attention(cabi, Hq, Hkv, D, splits):
+    lens = [1, 15, 16, 17, 100, 257, 1153]
+    kc, vc, bt, ks, vs = _paged_case(31 + Hq + D + splits, lens, Hq, Hkv, D)
+    B = len(lens)
+    g = torch.Generator().manual_seed(77)
+    q = _bf16(torch.randn(B, Hq, D, generator=g))
+    out = torch.empty(B, Hq * D, dtype=torch.bfloat16, device="cuda")
+    ws = torch.empty(max(1, cabi.decode_workspace_bytes(B, Hq, D, splits) // 4), device="cuda")
+    cabi.paged_attn_decode(q.cuda().view(B, Hq * D), kc.cuda(), vc.cuda(), bt.cuda(),
+                           torch.tensor(lens, dtype=torch.int32).cuda(), out, ws, B, Hq, Hkv, D, 16, splits,
+                           D ** -0.5)
+    got = out.float().cpu().view(B, Hq, D)
+    for b, L in enumerate(lens):
+        want = R.attention(q[b].float()[None], ks[b], vs[b], L - 1)[0]
+        # fp32 softmax/accumulate, one bf16 rounding of an O(1) output
+        assert torch.all((got[b] - want).abs() <= 2 ** -7 * want.abs() + 2e-3), (b, L)
+
+
+def test_paged_decode_zero_length_rows(cabi):
+    """Padded batch entries (seq_len 0) must produce zeros, not NaN."""
+    kc, vc, bt, ks, vs = _paged_case(5, [40, 40], 8, 2, 64)
+    q = _bf16(torch.randn(2, 8 * 64))
+    out = torch.full((2, 8 * 64), 9.0, dtype=torch.bfloat16, device="cuda")
+    ws = torch.empty(cabi.decode_workspace_bytes(2, 8, 64, 4) // 4, device="cuda")
+    cabi.paged_attn_decode(q.cuda(), kc.cuda(), vc.cuda(), bt.cuda(), torch.tensor([40, 0], dtype=torch.int32).cuda(),
+                           out, ws, 2, 8, 2, 64, 16, 4, 0.125)
+    assert torch.all(out[1] == 0) and torch.isfinite(out.float()).all()
+
+
+@pytest.mark.parametrize("Hq,Hkv,D", [(32, 8, 128), (8, 2, 64)])
+def test_paged_prefill_attention(cabi, Hq, Hkv, D):
+    # (context length incl. chunk, chunk length): fresh prompts, chunked continuation, prefix hit, 1-token chunk
+    cases = [(64, 64), (200, 200), (333, 77), (1024, 256), (17, 1), (130, 130)]
+    lens = [c for c, _ in cases]
+    kc, vc, bt, ks, vs = _paged_case(41 + D, lens, Hq, Hkv, D)
+    g = torch.Generator().manual_seed(78)
+    nq = [n for _, n in cases]
+    cu = [0]
+    for n in nq:
+        cu.append(cu[-1] + n)
+    T = cu[-1]
+    q = _bf16(torch.randn(T, Hq, D, generator=g))
+    out = torch.full((T, Hq * D), float("nan"), dtype=torch.bfloat16, device="cuda")
+    cabi.paged_attn_prefill(q.cuda().view(T, Hq * D), kc.cuda(), vc.cuda(), bt.cuda(),
+                            torch.tensor(cu, dtype=torch.int32).cuda(), torch.tensor(lens, dtype=torch.int32).cuda(),
+                            out, len(cases), max(nq), Hq, Hkv, D, 16, D ** -0.5)
+    got = out.float().cpu().view(T, Hq, D)
+    for i, (ctx, n) in enumerate(cases):
+        want = R.attention(q[cu[i]:cu[i + 1]].float(), ks[i], vs[i], ctx - n)
+        err = (got[cu[i]:cu[i + 1]] - want).abs()
+        # P is rounded to bf16 before P.V (2^-9 relative per term) + bf16 output rounding
+        assert torch.all(err <= 2 ** -6 * want.abs() + 6e-3), (i, float(err.max()))
+
+
+# ------------------------------------------------------------------------------------- sampler
+def test_argmax_exact_and_tie_break(cabi):
+    g = torch.Generator().manual_seed(1)
+    V = 128256
+    logits = torch.randn(5, V, generator=g)
+    logits[2, 777] = logits[2, 99999] = 50.0  # tie: lowest index wins (torch.argmax)
+    logits[3, V - 1] = 60.0
+    out = torch.empty(5, dtype=torch.int32, device="cuda")
+    cabi.sample(logits.cuda(), out, 5, V)
+    assert out.cpu().tolist() == torch.argmax(logits, dim=-1).tolist()
+    assert out[2].item() == 777
+
+
+def test_temperature_sampling_matches_oracle_stream(cabi):
+    V, B = 4096, 16
+    g = torch.Generator().manual_seed(2)
+    logits = torch.randn(B, V, generator=g) * 2
+    temps = torch.full((B,), 0.7)
+    temps[0] = 0.0
+    seeds = torch.arange(B, dtype=torch.int64) * 7919 + (1 << 40)
+    steps = torch.arange(B, dtype=torch.int32)
+    out = torch.empty(B, dtype=torch.int32, device="cuda")
+    cabi.sample(logits.cuda(), out, B, V, temps.cuda(), None, seeds.cuda(), steps.cuda())
+    ids = out.cpu().tolist()
+    assert ids[0] == int(torch.argmax(logits[0]))
+    for b in range(1, B):
+        sc = SR.sample_scores(logits[b].numpy(), 0.7, int(seeds[b]), int(steps[b]))
+        # logf on the device may differ from numpy by an ulp: the chosen id must be the oracle's
+        # arg-max up to 1e-4 in score
+        assert sc[ids[b]] >= sc.max() - 1e-4, b
+
+
+def test_temperature_sampling_distribution(cabi):
+    """Chi-square style check of the draw against softmax(l / T) on a small vocabulary."""
+    V, N = 8, 4096
+    logits = torch.tensor([[2.0, 1.0, 0.5, 0.0, -0.5, -1.0, -3.0, 1.5]]).repeat(N, 1)
+    temps = torch.full((N,), 0.8)
+    seeds = torch.arange(N, dtype=torch.int64) + 12345
+    steps = torch.zeros(N, dtype=torch.int32)
+    out = torch.empty(N, dtype=torch.int32, device="cuda")
+    cabi.sample(logits.cuda(), out, N, V, temps.cuda(), None, seeds.cuda(), steps.cuda())
+    freq = np.bincount(out.cpu().numpy(), minlength=V) / N
+    p = torch.softmax(logits[0] / 0.8, -1).numpy()
+    assert np.all(np.abs(freq - p) < 4 * np.sqrt(p * (1 - p) / N) + 2e-3), (freq, p)
+
+
+def test_top_p_restricts_to_nucleus(cabi):
+    V, N = 64, 512
+    g = torch.Generator().manual_seed(4)
+    row = torch.randn(V, generator=g) * 3
+    logits = row.repeat(N, 1)
+    T, P = 1.0, 0.6
+    keep = SR.nucleus_mask(row.numpy(), T, P)
+    out = torch.empty(N, dtype=torch.int32, device="cuda")
+    cabi.sample(logits.cuda(), out, N, V, torch.full((N,), T).cuda(), torch.full((N,), P).cuda(),
+                (torch.arange(N, dtype=torch.int64) + 99).cuda(), torch.zeros(N, dtype=torch.int32).cuda())
+    ids = out.cpu().numpy()
+    assert keep[ids].all()
+    assert len(set(ids.tolist())) == keep.sum() or keep.sum() > 8  # every nucleus token is reachable
