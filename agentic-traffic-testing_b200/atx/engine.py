@@ -1,0 +1,197 @@
+"""LLMEngine (synchronous step loop) and AsyncEngine (the `AsyncLLMEngine`-shaped facade).
+
+`AsyncEngine.generate(prompt_token_ids, sampling_params, request_id)` is an async generator
+yielding RequestOutput objects as tokens arrive — the same consumption pattern as
+`AsyncLLMEngine.generate` in llm/serve_llm.py:527-561 (first yielded output = time to first token).
+One engine thread per GPU issues every CUDA launch; the asyncio side never blocks on the device.
+"""
+from __future__ import annotations
+
+import asyncio
+import threading
+import time
+from dataclasses import dataclass, field
+from typing import AsyncIterator, Callable, Dict, List, Optional, Sequence as Seq
+
+import torch
+
+from .config import EngineConfig, ModelConfig, ModelSource, resolve_model
+from .kv_cache import BlockAllocator
+from .runner import ModelRunner
+from .scheduler import SamplingParams, Scheduler, Sequence, SeqState
+from .weights import ModelWeights
+
+
+@dataclass
+class RequestOutput:
+    request_id: str
+    token_ids: List[int]            # all generated ids so far
+    new_token_ids: List[int]
+    finished: bool
+    finish_reason: Optional[str]
+    prompt_len: int
+    num_cached_tokens: int = 0
+    ttft_s: Optional[float] = None
+
+
+class LLMEngine:
+    def __init__(self, source: ModelSource, ecfg: EngineConfig, weights: Optional[ModelWeights] = None):
+        self.mcfg: ModelConfig = source.config
+        self.ecfg = ecfg
+        dev = torch.device("cuda", ecfg.device)
+        torch.cuda.set_device(dev)
+        if weights is None:
+            if source.path is not None:
+                weights = ModelWeights.from_hf_dir(self.mcfg, source.path, dev)
+            else:
+                weights = ModelWeights.random(self.mcfg, source.random_seed or 0, dev)
+        self.runner = ModelRunner(self.mcfg, ecfg, weights)
+        self.allocator = BlockAllocator(self.runner.num_blocks, ecfg.block_size, ecfg.enable_prefix_caching)
+        self.scheduler = Scheduler(self.allocator, ecfg.max_num_seqs, ecfg.max_num_batched_tokens, ecfg.max_model_len,
+                                   self.mcfg.eos_token_ids)
+        self.steps = 0
+        self.batch_size_observer: Optional[Callable[[int], None]] = None
+
+    def add_request(self, request_id: str, prompt_ids: Seq[int], params: SamplingParams) -> Sequence:
+        V = self.mcfg.vocab_size
+        if any((t < 0 or t >= V) for t in prompt_ids):
+            raise ValueError("prompt token id outside the vocabulary")
+        budget = self.ecfg.max_model_len - len(prompt_ids)
+        if budget <= 0:
+            raise ValueError(f"prompt of {len(prompt_ids)} tokens does not fit max_model_len={self.ecfg.max_model_len}")
+        if params.max_tokens > budget:
+            params = SamplingParams(**{**params.__dict__, "max_tokens": budget})
+        seq = Sequence(request_id, prompt_ids, params, self.allocator)
+        self.scheduler.add(seq)
+        return seq
+
+    def abort(self, request_id: str) -> None:
+        self.scheduler.abort(request_id)
+
+    def has_work(self) -> bool:
+        return self.scheduler.has_work()
+
+    def step(self) -> List[Sequence]:
+        """One scheduler + forward pass. Returns sequences that received a token."""
+        plan = self.scheduler.schedule()
+        if plan.empty:
+            return []
+        if self.batch_size_observer is not None:
+            self.batch_size_observer(len(plan.decodes) + len(plan.prefills))
+        sampled = self.runner.execute(plan)
+        self.steps += 1
+        return self.scheduler.commit(plan, sampled)
+
+    def generate_sync(self, prompts: List[Seq[int]], params: SamplingParams) -> List[List[int]]:
+        """Blocking helper for tests and the bench: run the given prompts to completion."""
+        seqs = [self.add_request(f"sync-{i}-{id(prompts)}", p, params) for i, p in enumerate(prompts)]
+        while self.has_work():
+            self.step()
+        return [s.output_ids for s in seqs]
+
+
+class _Stream:
+    __slots__ = ("queue", "loop", "seq", "submitted")
+
+    def __init__(self, loop: asyncio.AbstractEventLoop):
+        self.queue: asyncio.Queue = asyncio.Queue()
+        self.loop = loop
+        self.seq: Optional[Sequence] = None
+        self.submitted = time.monotonic()
+
+
+class AsyncEngine:
+    """Thread-backed engine with an asyncio streaming interface (one per GPU / replica)."""
+
+    def __init__(self, engine: LLMEngine):
+        self.engine = engine
+        self._inbox: List = []
+        self._cv = threading.Condition()
+        self._streams: Dict[str, _Stream] = {}
+        self._stop = False
+        self._error: Optional[BaseException] = None
+        self._thread = threading.Thread(target=self._run, name="atx-engine", daemon=True)
+        self._thread.start()
+
+    # ---- asyncio side -----------------------------------------------------------------------------
+    async def generate(self, prompt_ids: Seq[int], params: SamplingParams, request_id: str
+                       ) -> AsyncIterator[RequestOutput]:
+        if self._error is not None:
+            raise RuntimeError(f"engine thread died: {self._error!r}")
+        loop = asyncio.get_running_loop()
+        st = _Stream(loop)
+        with self._cv:
+            if request_id in self._streams:
+                raise ValueError(f"duplicate request id {request_id!r}")
+            self._streams[request_id] = st
+            self._inbox.append(("add", request_id, list(prompt_ids), params))
+            self._cv.notify()
+        try:
+            while True:
+                item = await st.queue.get()
+                if isinstance(item, BaseException):
+                    raise item
+                yield item
+                if item.finished:
+                    return
+        finally:
+            with self._cv:
+                if self._streams.pop(request_id, None) is not None and (st.seq is None or
+                                                                         st.seq.state is not SeqState.FINISHED):
+                    self._inbox.append(("abort", request_id))  # client went away: free the KV blocks
+                    self._cv.notify()
+
+    def shutdown(self) -> None:
+        with self._cv:
+            self._stop = True
+            self._cv.notify()
+        self._thread.join(timeout=10)
+
+    # ---- engine thread ----------------------------------------------------------------------------
+    def _post(self, st: _Stream, item) -> None:
+        st.loop.call_soon_threadsafe(st.queue.put_nowait, item)
+
+    def _run(self) -> None:
+        eng = self.engine
+        try:
+            torch.cuda.set_device(eng.runner.dev)
+            while True:
+                with self._cv:
+                    while not self._inbox and not eng.has_work() and not self._stop:
+                        self._cv.wait()
+                    if self._stop:
+                        return
+                    inbox, self._inbox = self._inbox, []
+                for msg in inbox:
+                    if msg[0] == "add":
+                        _, rid, ids, params = msg
+                        st = self._streams.get(rid)
+                        if st is None:
+                            continue
+                        try:
+                            st.seq = eng.add_request(rid, ids, params)
+                        except Exception as exc:  # bad request: surface to the awaiting handler
+                            self._post(st, exc)
+                    else:
+                        eng.abort(msg[1])
+                if not eng.has_work():
+                    continue
+                for seq in eng.step():
+                    st = self._streams.get(seq.request_id)
+                    if st is None:
+                        continue
+                    fin = seq.state is SeqState.FINISHED
+                    out = seq.output_ids
+                    ttft = (seq.first_token_time - seq.arrival) if seq.first_token_time else None
+                    self._post(st, RequestOutput(seq.request_id, out, out[-1:], fin, seq.finish_reason,
+                                                 seq.prompt_len, seq.cached_prompt_tokens, ttft))
+        except BaseException as exc:  # device fault etc.: fail every waiter loudly, never hang them
+            self._error = exc
+            with self._cv:
+                streams = list(self._streams.values())
+            for st in streams:
+                self._post(st, RuntimeError(f"engine failure: {exc!r}"))
+
+
+def build_engine(model: str, ecfg: EngineConfig, weights: Optional[ModelWeights] = None) -> LLMEngine:
+    return LLMEngine(resolve_model(model), ecfg, weights)

@@ -1,0 +1,350 @@
+"""ModelRunner: executes one scheduler step (a flat batch of decode tokens + prompt chunks) on one
+B200 by calling the C-ABI kernels; owns the weights, the paged KV pools and every activation buffer.
+
+This is the part of vLLM's model runner that the reference reaches through
+`AsyncLLMEngine.generate` (llm/serve_llm.py:527), rebuilt B200-first:
+  * all buffers are allocated once (no allocator traffic on the hot path, CUDA-graph safe),
+  * decode-only steps replay a CUDA graph per (batch bucket, KV-split bucket),
+  * every kernel is launched with programmatic dependent launch so that a GEMM's weight
+    prefetch overlaps the tail of the kernel before it,
+  * host inputs go through one pinned staging buffer; the only device->host traffic per step is
+    the sampled token ids.
+Layer schedule (per token batch of T rows; h is the fp32 residual stream):
+  xn = rmsnorm(h)            -> bf16      (also clears the split-K accumulator that follows)
+  qkv = xn @ Wqkv^T          -> fp32      (tcgen05 GEMM, split-K for decode)
+  q, K/V pages = rope(qkv)   -> bf16      (scatter by slot mapping)
+  a = paged attention        -> bf16
+  h += a @ Wo^T                            (GEMM epilogue adds into the residual)
+  xn = rmsnorm(h); gu = xn @ Wgu^T; act = silu(g) * u; h += act @ Wdown^T
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from typing import Dict, List, Optional, Tuple
+
+import numpy as np
+import torch
+
+from . import _cabi
+from .config import EngineConfig, ModelConfig
+from .scheduler import Chunk, StepPlan
+from .weights import ModelWeights, rope_table
+
+_GRAPH_BUCKETS = [1, 2, 4, 6, 8, 12, 16, 24, 32, 48, 64]
+
+
+def _bucket(n: int, buckets: List[int]) -> Optional[int]:
+    for b in buckets:
+        if n <= b:
+            return b
+    return None
+
+
+class ModelRunner:
+    def __init__(self, mcfg: ModelConfig, ecfg: EngineConfig, weights: ModelWeights):
+        if not torch.cuda.is_available():
+            raise RuntimeError("atx ModelRunner needs a CUDA device (there is no CPU fallback)")
+        self.lib = _cabi.load()
+        self.m, self.e, self.w = mcfg, ecfg, weights
+        self.dev = weights.device
+        torch.cuda.set_device(self.dev)
+        m, e = mcfg, ecfg
+        self.Tmax = max(16, e.max_num_batched_tokens)
+        self.Smax = max(1, e.max_num_seqs)
+        self.bs = e.block_size
+        self.MB = (e.max_model_len + self.bs - 1) // self.bs
+        H, I, V = m.hidden_size, m.intermediate_size, m.vocab_size
+        bf, f32, i32 = torch.bfloat16, torch.float32, torch.int32
+        dev = self.dev
+        T, S = self.Tmax, max(self.Smax, 16)
+        self.h = torch.zeros(T, H, dtype=f32, device=dev)
+        self.xn = torch.zeros(T, H, dtype=bf, device=dev)
+        self.qkv = torch.zeros(T, m.qkv_size, dtype=f32, device=dev)
+        self.q = torch.zeros(T, m.q_size, dtype=bf, device=dev)
+        self.attn = torch.zeros(T, m.q_size, dtype=bf, device=dev)
+        self.gu = torch.zeros(T, 2 * I, dtype=f32, device=dev)
+        self.act = torch.zeros(T, I, dtype=bf, device=dev)
+        self.xl = torch.zeros(S, H, dtype=bf, device=dev)
+        self.logits = torch.zeros(S, V, dtype=f32, device=dev)
+        self.out_ids = torch.zeros(S, dtype=i32, device=dev)
+        self.out_host = torch.zeros(S, dtype=i32).pin_memory()
+        self.rope = rope_table(m, e.max_model_len, dev)
+        self.max_splits = 32
+        self.ws = torch.zeros(max(1, _cabi.decode_workspace_bytes(S, m.num_attention_heads, m.head_dim,
+                                                                  self.max_splits) // 4), dtype=f32, device=dev)
+
+        # ---- staged integer / float inputs: one pinned host mirror, one device buffer -----------
+        S_ = self.Smax
+        off, self._off = 0, {}
+
+        def region(name: str, n: int) -> None:
+            nonlocal off
+            off = (off + 3) // 4 * 4  # 16-byte aligned regions
+            self._off[name] = (off, n)
+            off += n
+
+        for name, n in (("ids", T), ("pos", T), ("slots", T), ("dec_lens", S_), ("pf_cu", S_ + 1), ("pf_ctx", S_),
+                        ("rows", S_), ("steps", S_), ("temps", S_), ("top_p", S_), ("seeds", 2 * S_),
+                        ("dec_bt", S_ * self.MB), ("pf_bt", S_ * self.MB)):
+            region(name, n)
+        self._meta_lo = self._off["dec_lens"][0]
+        self._meta_hi = self._off["seeds"][0] + self._off["seeds"][1]
+        self.hbuf = torch.zeros(off, dtype=i32).pin_memory()
+        self.dbuf = torch.zeros(off, dtype=i32, device=dev)
+        self.hnp = self.hbuf.numpy()
+        self._hv = {k: self.hnp[o:o + n] for k, (o, n) in self._off.items()}
+        self._hv["temps_f"] = self._hv["temps"].view(np.float32)
+        self._hv["top_p_f"] = self._hv["top_p"].view(np.float32)
+        self._hv["seeds_q"] = self._hv["seeds"].view(np.int64)
+        self._hv["dec_bt2"] = self._hv["dec_bt"].reshape(S_, self.MB)
+        self._hv["pf_bt2"] = self._hv["pf_bt"].reshape(S_, self.MB)
+        base = self.dbuf.data_ptr()
+        self._dp = {k: base + 4 * o for k, (o, n) in self._off.items()}
+
+        # ---- GEMM plans (TMA descriptors) --------------------------------------------------------
+        self.plans = []
+        for l in weights.layers:
+            self.plans.append((_cabi.GemmPlan(l.wqkv, self.xn), _cabi.GemmPlan(l.wo, self.attn),
+                               _cabi.GemmPlan(l.wgu, self.xn), _cabi.GemmPlan(l.wdown, self.act)))
+        self.plan_lm = _cabi.GemmPlan(weights.lm_head, self.xl)
+
+        # ---- paged KV pools, sized from what is left of the HBM budget ---------------------------
+        self.block_bytes = 2 * m.num_hidden_layers * m.num_key_value_heads * self.bs * m.head_dim * 2
+        if e.num_gpu_blocks is not None:
+            nb = int(e.num_gpu_blocks)
+        else:
+            free, total = torch.cuda.mem_get_info(dev)
+            budget = int(total * e.gpu_memory_utilization) - (total - free) - (512 << 20)
+            nb = budget // self.block_bytes
+            if nb < self.MB:
+                raise RuntimeError(f"KV budget {budget / 2**30:.1f} GiB holds {nb} blocks; one sequence of "
+                                   f"max_model_len={e.max_model_len} needs {self.MB}")
+        self.num_blocks = nb
+        L, Hkv, D = m.num_hidden_layers, m.num_key_value_heads, m.head_dim
+        self.k_cache = torch.zeros(L, nb, Hkv, self.bs, D, dtype=bf, device=dev)
+        self.v_cache = torch.zeros(L, nb, Hkv, self.bs, D, dtype=bf, device=dev)
+
+        self._graphs: Dict[Tuple[int, int], torch.cuda.CUDAGraph] = {}
+        self._graph_launches: Dict[Tuple[int, int], int] = {}
+        self.stream = torch.cuda.Stream(device=dev)   # every launch and copy of this runner
+        self._h2d_done = torch.cuda.Event()
+        self.flags = _cabi.FLAG_PDL if e.use_pdl else 0
+        self.scale = float(m.head_dim) ** -0.5
+        self.launches_last_step = 0
+        self.kernel_launches = 0  # cumulative count of our kernels launched (graph replays included)
+        self.h2d_bytes = 0
+        self.d2h_bytes = 0
+
+    # ----------------------------------------------------------------------------------------------
+    def _ck(self, rc: int) -> None:
+        if rc != 0:
+            raise _cabi.AtxError(f"atx error {rc}: {self.lib.atx_last_error().decode()}")
+
+    def _forward(self, T: int, n_dec: int, dec_splits: int, n_pf: int, max_q: int, n_rows: int) -> int:
+        """Issue every kernel of one step on the current stream. Returns the launch count."""
+        lib, m, w, ck = self.lib, self.m, self.w, self._ck
+        st = torch.cuda.current_stream().cuda_stream
+        fl = self.flags
+        H, I, V = m.hidden_size, m.intermediate_size, m.vocab_size
+        Hq, Hkv, D = m.num_attention_heads, m.num_key_value_heads, m.head_dim
+        dp = self._dp
+        h, xn, qkv, q, attn, gu, act = (t.data_ptr() for t in (self.h, self.xn, self.qkv, self.q, self.attn,
+                                                                self.gu, self.act))
+        n = 0
+        ck(lib.atx_embed_gather(dp["ids"], w.embed.data_ptr(), h, T, H, V, st))
+        n += 1
+        sp_qkv = lib.atx_gemm_auto_splits(m.qkv_size, H, T)
+        sp_gu = lib.atx_gemm_auto_splits(2 * I, H, T)
+        qb = m.q_size * 2  # bytes per row of q / attn
+        for li, l in enumerate(w.layers):
+            p_qkv, p_o, p_gu, p_down = self.plans[li]
+            kc, vc = self.k_cache[li].data_ptr(), self.v_cache[li].data_ptr()
+            if sp_qkv > 1:
+                ck(lib.atx_rmsnorm(h, None, l.ln1.data_ptr(), xn, T, H, m.rms_norm_eps, qkv, T * m.qkv_size * 4, fl, st))
+                ck(lib.atx_gemm_run(p_qkv._h, qkv, m.qkv_size, T, _cabi.GEMM_ADD_F32, sp_qkv, fl, st))
+            else:
+                ck(lib.atx_rmsnorm(h, None, l.ln1.data_ptr(), xn, T, H, m.rms_norm_eps, None, 0, fl, st))
+                ck(lib.atx_gemm_run(p_qkv._h, qkv, m.qkv_size, T, _cabi.GEMM_STORE_F32, 1, fl, st))
+            ck(lib.atx_rope_kv_write(qkv, dp["pos"], dp["slots"], self.rope.data_ptr(), q, kc, vc, T, Hq, Hkv, D,
+                                     self.bs, fl, st))
+            n += 3
+            if n_dec:
+                ck(lib.atx_paged_attn_decode(q, kc, vc, dp["dec_bt"], dp["dec_lens"], attn, self.ws.data_ptr(),
+                                             self.ws.numel() * 4, n_dec, Hq, Hkv, D, self.bs, self.MB, dec_splits,
+                                             self.scale, fl, st))
+                n += 2 if dec_splits > 1 else 1
+            if n_pf:
+                ck(lib.atx_paged_attn_prefill(q + n_dec * qb, kc, vc, dp["pf_bt"], dp["pf_cu"], dp["pf_ctx"],
+                                              attn + n_dec * qb, n_pf, max_q, Hq, Hkv, D, self.bs, self.MB,
+                                              self.scale, fl, st))
+                n += 1
+            ck(lib.atx_gemm_run(p_o._h, h, H, T, _cabi.GEMM_ADD_F32, 0, fl, st))
+            if sp_gu > 1:
+                ck(lib.atx_rmsnorm(h, None, l.ln2.data_ptr(), xn, T, H, m.rms_norm_eps, gu, T * 2 * I * 4, fl, st))
+                ck(lib.atx_gemm_run(p_gu._h, gu, 2 * I, T, _cabi.GEMM_ADD_F32, sp_gu, fl, st))
+            else:
+                ck(lib.atx_rmsnorm(h, None, l.ln2.data_ptr(), xn, T, H, m.rms_norm_eps, None, 0, fl, st))
+                ck(lib.atx_gemm_run(p_gu._h, gu, 2 * I, T, _cabi.GEMM_STORE_F32, 1, fl, st))
+            ck(lib.atx_silu_mul(gu, act, T, I, fl, st))
+            ck(lib.atx_gemm_run(p_down._h, h, H, T, _cabi.GEMM_ADD_F32, 0, fl, st))
+            n += 5
+        if n_rows:
+            ck(lib.atx_rmsnorm(h, dp["rows"], w.norm.data_ptr(), self.xl.data_ptr(), n_rows, H, m.rms_norm_eps, None,
+                               0, fl, st))
+            ck(lib.atx_gemm_run(self.plan_lm._h, self.logits.data_ptr(), V, n_rows, _cabi.GEMM_STORE_F32, 1, fl, st))
+            ck(lib.atx_sample(self.logits.data_ptr(), V, dp["temps"], dp["top_p"], dp["seeds"], dp["steps"],
+                              self.out_ids.data_ptr(), n_rows, V, fl, st))
+            n += 3
+        return n
+
+    # ----------------------------------------------------------------------------------------------
+    def _h2d(self, name: str, count: int) -> None:
+        o, _ = self._off[name]
+        self.dbuf[o:o + count].copy_(self.hbuf[o:o + count], non_blocking=True)
+        self.h2d_bytes += 4 * count
+
+    def decode_splits(self, n_dec: int, max_len: int) -> int:
+        """KV partitions per sequence: enough CTAs to cover the SMs, >= 256 tokens per partition."""
+        if n_dec == 0:
+            return 1
+        want = max(1, (2 * 148) // max(1, n_dec * self.m.num_key_value_heads))
+        by_len = max(1, max_len // 256)
+        s = 1
+        while s * 2 <= min(want, by_len, self.max_splits):
+            s *= 2
+        return s
+
+    def execute(self, plan: StepPlan) -> Dict[int, int]:
+        """Run one step; returns {Sequence.uid: sampled token id} for every chunk that samples."""
+        with torch.cuda.stream(self.stream):
+            return self._execute(plan)
+
+    def _execute(self, plan: StepPlan) -> Dict[int, int]:
+        self._h2d_done.synchronize()  # the previous step's staging copies have left the pinned buffer
+        hv, bs = self._hv, self.bs
+        decs, pfs = plan.decodes, plan.prefills
+        n_dec, n_pf = len(decs), len(pfs)
+        T_real = n_dec + sum(c.count for c in pfs)
+        if T_real == 0:
+            return {}
+        if T_real > self.Tmax or n_dec + n_pf > self.Smax:
+            raise RuntimeError("step exceeds the runner's static capacity")
+        use_graph = self.e.enable_cuda_graphs and n_pf == 0 and _bucket(n_dec, _GRAPH_BUCKETS) is not None \
+            and _bucket(n_dec, _GRAPH_BUCKETS) <= self.Smax
+        B = _bucket(n_dec, _GRAPH_BUCKETS) if use_graph else n_dec
+        T = B + (T_real - n_dec)
+
+        ids, pos, slots = hv["ids"], hv["pos"], hv["slots"]
+        rows: List[int] = []
+        sampling: List[Chunk] = []
+        max_len = 0
+        for i, c in enumerate(decs):
+            s = c.seq
+            p = c.start
+            ids[i] = s.tokens[p]
+            pos[i] = p
+            tbl = s.blocks.table
+            slots[i] = tbl[p // bs] * bs + p % bs
+            hv["dec_bt2"][i, :len(tbl)] = tbl
+            hv["dec_lens"][i] = p + 1
+            max_len = max(max_len, p + 1)
+            rows.append(i)
+            sampling.append(c)
+        for i in range(n_dec, B):  # graph padding: no KV write, empty attention, ignored sample
+            ids[i] = 0
+            pos[i] = 0
+            slots[i] = -1
+            hv["dec_lens"][i] = 0
+            rows.append(i)
+        o = B
+        max_q = 0
+        hv["pf_cu"][0] = 0
+        for j, c in enumerate(pfs):
+            s = c.seq
+            a, n = c.start, c.count
+            ids[o:o + n] = s.tokens[a:a + n]
+            pr = np.arange(a, a + n, dtype=np.int32)
+            pos[o:o + n] = pr
+            tbl = np.asarray(s.blocks.table, dtype=np.int32)
+            slots[o:o + n] = tbl[pr // bs] * bs + pr % bs
+            hv["pf_bt2"][j, :len(tbl)] = tbl
+            hv["pf_cu"][j + 1] = o - B + n
+            hv["pf_ctx"][j] = a + n
+            max_q = max(max_q, n)
+            if c.samples:
+                rows.append(o + n - 1)
+                sampling.append(c)
+            o += n
+        n_rows = len(rows)
+        hv["rows"][:n_rows] = rows
+        k = 0
+        for r, c in enumerate(sampling):
+            s = c.seq
+            # padded graph rows sit between decodes and prefill rows: map sampling index -> row slot
+            slot_r = r if r < n_dec else (B - n_dec) + r
+            hv["temps_f"][slot_r] = s.params.temperature
+            hv["top_p_f"][slot_r] = s.params.top_p
+            hv["seeds_q"][slot_r] = s.seed
+            hv["steps"][slot_r] = s.num_generated
+            k += 1
+        for i in range(n_dec, B):
+            hv["temps_f"][i] = 0.0
+            hv["top_p_f"][i] = 1.0
+
+        # ---- host -> device (pinned, async on the compute stream) --------------------------------
+        self._h2d("ids", T)
+        self._h2d("pos", T)
+        self._h2d("slots", T)
+        lo, hi = self._meta_lo, self._meta_hi
+        self.dbuf[lo:hi].copy_(self.hbuf[lo:hi], non_blocking=True)
+        self.h2d_bytes += 4 * (hi - lo)
+        if n_dec:
+            self._h2d("dec_bt", n_dec * self.MB)
+        if n_pf:
+            self._h2d("pf_bt", n_pf * self.MB)
+        self._h2d_done.record()
+
+        splits = self.decode_splits(B, max_len)
+        if use_graph:
+            key = (B, splits)
+            g = self._graphs.get(key)
+            if g is None:
+                g = self._capture(B, splits)
+            g.replay()
+            self.launches_last_step = self._graph_launches[key]
+        else:
+            self.launches_last_step = self._forward(T, B, splits, n_pf, max_q, n_rows)
+        self.kernel_launches += self.launches_last_step
+
+        out: Dict[int, int] = {}
+        if n_rows:
+            self.out_host[:n_rows].copy_(self.out_ids[:n_rows], non_blocking=True)
+            self.d2h_bytes += 4 * n_rows
+            torch.cuda.current_stream().synchronize()
+            oh = self.out_host.numpy()
+            for r, c in enumerate(sampling):
+                slot_r = r if r < n_dec else (B - n_dec) + r
+                out[c.seq.uid] = int(oh[slot_r])
+        return out
+
+    def _capture(self, B: int, splits: int) -> torch.cuda.CUDAGraph:
+        """Capture one decode step for batch bucket B. Inputs already sit in dbuf; the warm-up run
+        writes the same K/V slots and logits the replay will write again, so it is harmless."""
+        torch.cuda.current_stream().synchronize()
+        s = torch.cuda.Stream(device=self.dev)
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            self._forward(B, B, splits, 0, 0, B)  # warm-up: sets func attributes outside capture
+        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.synchronize(self.dev)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=s):
+            n = self._forward(B, B, splits, 0, 0, B)
+        self._graphs[(B, splits)] = g
+        self._graph_launches[(B, splits)] = n
+        return g
+
+    # ---- capacity facts for the server's gauges ---------------------------------------------------
+    def kv_cache_info(self) -> Tuple[int, int]:
+        return self.num_blocks, self.bs

@@ -1,0 +1,155 @@
+"""Device-resident Llama weights in the layout the kernels stream.
+
+HF state-dict names (transformers LlamaForCausalLM) are fused per layer into
+  wqkv  [(Hq + 2 Hkv) * D, H]   = cat(q_proj, k_proj, v_proj)      one GEMM, one pass over x
+  wo    [H, Hq * D]
+  wgu   [2 I, H]                = cat(gate_proj, up_proj)           one GEMM
+  wdown [H, I]
+all bf16 row-major [out_features, in_features] (the layout torch.nn.Linear / HF store, K-major for
+the tcgen05 GEMM, so no transposition ever happens).
+"""
+from __future__ import annotations
+
+from pathlib import Path
+from typing import Dict, List, Optional
+
+import torch
+
+from .config import ModelConfig
+
+
+class LayerWeights:
+    __slots__ = ("ln1", "wqkv", "wo", "ln2", "wgu", "wdown")
+
+    def __init__(self):
+        self.ln1 = self.wqkv = self.wo = self.ln2 = self.wgu = self.wdown = None
+
+
+class ModelWeights:
+    def __init__(self, cfg: ModelConfig, device: torch.device):
+        self.cfg = cfg
+        self.device = device
+        self.embed: torch.Tensor = None      # [V, H] bf16
+        self.layers: List[LayerWeights] = []
+        self.norm: torch.Tensor = None       # [H] bf16
+        self.lm_head: torch.Tensor = None    # [V, H] bf16 (aliases embed when tied)
+
+    def nbytes(self) -> int:
+        seen, total = set(), 0
+        for t in self._all():
+            if t.data_ptr() not in seen:
+                seen.add(t.data_ptr())
+                total += t.numel() * t.element_size()
+        return total
+
+    def _all(self):
+        yield self.embed
+        yield self.norm
+        yield self.lm_head
+        for l in self.layers:
+            yield from (l.ln1, l.wqkv, l.wo, l.ln2, l.wgu, l.wdown)
+
+    # ---- constructors ---------------------------------------------------------------------------
+    @classmethod
+    def from_state_dict(cls, cfg: ModelConfig, sd: Dict[str, torch.Tensor], device: torch.device) -> "ModelWeights":
+        """`sd` uses HF names; values may be fp32/bf16 on any device."""
+        w = cls(cfg, device)
+
+        def dev(t: torch.Tensor) -> torch.Tensor:
+            return t.to(device=device, dtype=torch.bfloat16).contiguous()
+
+        w.embed = dev(sd["model.embed_tokens.weight"])
+        for i in range(cfg.num_hidden_layers):
+            p = f"model.layers.{i}."
+            l = LayerWeights()
+            l.ln1 = dev(sd[p + "input_layernorm.weight"])
+            l.wqkv = dev(torch.cat([sd[p + "self_attn.q_proj.weight"], sd[p + "self_attn.k_proj.weight"],
+                                    sd[p + "self_attn.v_proj.weight"]], dim=0))
+            l.wo = dev(sd[p + "self_attn.o_proj.weight"])
+            l.ln2 = dev(sd[p + "post_attention_layernorm.weight"])
+            l.wgu = dev(torch.cat([sd[p + "mlp.gate_proj.weight"], sd[p + "mlp.up_proj.weight"]], dim=0))
+            l.wdown = dev(sd[p + "mlp.down_proj.weight"])
+            w.layers.append(l)
+        w.norm = dev(sd["model.norm.weight"])
+        w.lm_head = w.embed if cfg.tie_word_embeddings or "lm_head.weight" not in sd else dev(sd["lm_head.weight"])
+        w._check()
+        return w
+
+    @classmethod
+    def random(cls, cfg: ModelConfig, seed: int, device: torch.device, std: float = 0.02) -> "ModelWeights":
+        """Seeded random init generated ON the device (16 GB for 8B in well under a second). Values
+        do not match the CPU-seeded oracle weights; parity tests use from_state_dict instead."""
+        w = cls(cfg, device)
+        g = torch.Generator(device=device).manual_seed(seed)
+        H, I = cfg.hidden_size, cfg.intermediate_size
+
+        def mat(n, k):
+            return (torch.randn(n, k, generator=g, device=device, dtype=torch.float32) * std).to(torch.bfloat16)
+
+        def vec(n):
+            return (1.0 + 0.1 * torch.randn(n, generator=g, device=device)).to(torch.bfloat16)
+
+        w.embed = mat(cfg.vocab_size, H)
+        for _ in range(cfg.num_hidden_layers):
+            l = LayerWeights()
+            l.ln1, l.wqkv, l.wo = vec(H), mat(cfg.qkv_size, H), mat(H, cfg.q_size)
+            l.ln2, l.wgu, l.wdown = vec(H), mat(2 * I, H), mat(H, I)
+            w.layers.append(l)
+        w.norm = vec(H)
+        w.lm_head = w.embed if cfg.tie_word_embeddings else mat(cfg.vocab_size, H)
+        w._check()
+        return w
+
+    @classmethod
+    def from_hf_dir(cls, cfg: ModelConfig, path: Path, device: torch.device) -> "ModelWeights":
+        """Load *.safetensors shards of an HF checkpoint directory (hub snapshot layout)."""
+        from safetensors import safe_open
+
+        files = sorted(Path(path).glob("*.safetensors"))
+        if not files:
+            raise FileNotFoundError(f"no *.safetensors under {path}")
+        sd: Dict[str, torch.Tensor] = {}
+        for f in files:
+            with safe_open(str(f), framework="pt", device="cpu") as sf:
+                for k in sf.keys():
+                    sd[k] = sf.get_tensor(k)
+        return cls.from_state_dict(cfg, sd, device)
+
+    def _check(self) -> None:
+        c = self.cfg
+        assert self.embed.shape == (c.vocab_size, c.hidden_size)
+        assert self.lm_head.shape == (c.vocab_size, c.hidden_size)
+        assert len(self.layers) == c.num_hidden_layers
+        for l in self.layers:
+            assert l.wqkv.shape == (c.qkv_size, c.hidden_size) and l.wo.shape == (c.hidden_size, c.q_size)
+            assert l.wgu.shape == (2 * c.intermediate_size, c.hidden_size)
+            assert l.wdown.shape == (c.hidden_size, c.intermediate_size)
+        if c.hidden_size % 64 or c.intermediate_size % 64 or c.q_size % 64:
+            raise ValueError("hidden / intermediate / q sizes must be multiples of 64 (GEMM K blocking)")
+        if c.head_dim not in (64, 128):
+            raise ValueError("head_dim must be 64 or 128")
+
+
+def rope_table(cfg: ModelConfig, max_pos: int, device: torch.device) -> torch.Tensor:
+    """[max_pos, head_dim] fp32 cos ++ sin table with Llama-3 frequency scaling, computed on the CPU
+    in fp32 exactly as transformers does (modeling_rope_utils.py:550-620, modeling_llama.py:124-135)
+    so that RoPE in the kernel is a table lookup of the reference's own values."""
+    import math
+
+    D = cfg.head_dim
+    inv_freq = 1.0 / (cfg.rope_theta ** (torch.arange(0, D, 2, dtype=torch.int64).to(torch.float32) / D))
+    sc = cfg.rope_scaling
+    if sc and sc.get("rope_type", "default") == "llama3":
+        factor, low, high = sc["factor"], sc["low_freq_factor"], sc["high_freq_factor"]
+        old = sc["original_max_position_embeddings"]
+        low_wl, high_wl = old / low, old / high
+        wl = 2 * math.pi / inv_freq
+        scaled = torch.where(wl > low_wl, inv_freq / factor, inv_freq)
+        smooth = (old / wl - low) / (high - low)
+        smoothed = (1 - smooth) * scaled / factor + smooth * scaled
+        medium = ~(wl < high_wl) * ~(wl > low_wl)
+        inv_freq = torch.where(medium, smoothed, scaled)
+    elif sc and sc.get("rope_type", "default") != "default":
+        raise ValueError(f"unsupported rope_type {sc.get('rope_type')!r}")
+    freqs = torch.arange(max_pos, dtype=torch.float32)[:, None] * inv_freq[None, :]
+    return torch.cat((freqs.cos(), freqs.sin()), dim=-1).contiguous().to(device)

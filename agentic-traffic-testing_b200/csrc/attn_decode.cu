@@ -70,6 +70,7 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __r
     __shared__ float sm_l[kDecWarps][G];
     __shared__ float sm_acc[kDecWarps][G][D];
 
+    pdl_launch_dependents();
     pdl_wait();
     const int g = blockIdx.x, b = blockIdx.y, sp = blockIdx.z;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -194,7 +195,6 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __r
         }
     }
     __syncthreads();
-    pdl_launch_dependents();
     // merge the warps; one (head, dim) item per thread-iteration
     for (int it = threadIdx.x; it < G * D; it += kDecThreads) {
         const int j = it / D, d = it % D;
@@ -224,6 +224,7 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __r
 // out[h, :] = sum_s o_s * 2^(m_s - M) / sum_s l_s * 2^(m_s - M)
 __global__ void attn_decode_reduce_kernel(const float* __restrict__ ws_o, const float* __restrict__ ws_ml,
                                           __nv_bfloat16* __restrict__ out, int D, int num_splits) {
+    pdl_launch_dependents();
     pdl_wait();
     const long long h = blockIdx.x;
     const float* ml = ws_ml + h * num_splits * 2;
@@ -238,7 +239,6 @@ __global__ void attn_decode_reduce_kernel(const float* __restrict__ ws_o, const 
         }
         out[h * D + d] = __float2bfloat16_rn(ls > 0.f ? o / ls : 0.f);
     }
-    pdl_launch_dependents();
 }
 
 template <int D, int G>

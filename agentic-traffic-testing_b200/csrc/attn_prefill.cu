@@ -68,6 +68,7 @@ attn_prefill_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __
     uint8_t* sK = smem + kPfBM * D * 2;  // 2 stages
     uint8_t* sV = sK + 2 * TILE;         // 2 stages
 
+    pdl_launch_dependents();
     pdl_wait();
     const int s = blockIdx.z, h = blockIdx.y;
     const int q_begin = cu_q[s];
@@ -219,7 +220,6 @@ attn_prefill_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __
         __syncthreads();  // everyone done with this stage before it is refilled
     }
     cp_async_wait<0>();
-    pdl_launch_dependents();
 
     // ---- normalise and store
 #pragma unroll

@@ -78,6 +78,9 @@ gemm_wt_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_acc = *tmem_slot;
+    // Let the next kernel in the stream start its own prologue (and, if it is a GEMM, its weight
+    // prefetch) now; it still waits for this grid to finish before touching activations.
+    pdl_launch_dependents();
 
     if (nkb > 0) {
         if (warp == 0) {
@@ -146,7 +149,7 @@ gemm_wt_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
         // ===== epilogue: all four warps; warp w owns TMEM lanes [32w, 32w+32) = weight rows
         mbar_wait(accum_bar, 0);
         tc_fence_after();
-        pdl_launch_dependents();
+        pdl_wait();  // `out` may be the residual stream written by the upstream grid
         const int n = n0 + warp * 32 + lane;
         const bool n_ok = n < N;
 #pragma unroll 1
@@ -247,11 +250,13 @@ template <int TN>
 static int launch_gemm(const atx_gemm_plan* p, int ti, void* out, long long ldo, int T, int mode,
                        int splits, int pdl, cudaStream_t stream) {
     using Cfg = GemmCfg<TN>;
-    static bool attr_done = false;  // per-instantiation; benign race (idempotent call)
-    if (!attr_done) {
+    static bool attr_done[64] = {false};  // per instantiation and device; benign race (idempotent call)
+    int dev = 0;
+    ATX_CUDA(cudaGetDevice(&dev));
+    if (dev >= 0 && dev < 64 && !attr_done[dev]) {
         ATX_CUDA(cudaFuncSetAttribute(gemm_wt_kernel<TN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                       Cfg::kSmemBytes));
-        attr_done = true;
+        attr_done[dev] = true;
     }
     const int kb_total = static_cast<int>(p->K / kBK);
     const int kb_per = (kb_total + splits - 1) / splits;

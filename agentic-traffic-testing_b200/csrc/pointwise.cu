@@ -11,6 +11,7 @@ namespace atx {
 __global__ void __launch_bounds__(128) embed_gather_kernel(const int* __restrict__ ids,
                                                            const uint4* __restrict__ table,
                                                            float4* __restrict__ out, int H, int V) {
+    pdl_launch_dependents();
     pdl_wait();
     const int t = blockIdx.x;
     int id = ids[t];
@@ -22,7 +23,6 @@ __global__ void __launch_bounds__(128) embed_gather_kernel(const int* __restrict
         dst[2 * i] = make_float4(bf16lo(v.x), bf16hi(v.x), bf16lo(v.y), bf16hi(v.y));
         dst[2 * i + 1] = make_float4(bf16lo(v.z), bf16hi(v.z), bf16lo(v.w), bf16hi(v.w));
     }
-    pdl_launch_dependents();
 }
 
 // ---- RMSNorm (modeling_llama.py:62-67) ---------------------------------------------------------------
@@ -34,6 +34,7 @@ rmsnorm_kernel(const float* __restrict__ x, const int* __restrict__ rows, const 
                uint2* __restrict__ out, int T, int H, float eps, uint4* __restrict__ zero_ptr,
                long long zero_vecs) {
     __shared__ float red[kNormThreads / 32];
+    pdl_launch_dependents();
     pdl_wait();
     if (blockIdx.x >= T) {
         // extra blocks: clear the accumulation buffer of the split-K GEMM that follows
@@ -41,7 +42,6 @@ rmsnorm_kernel(const float* __restrict__ x, const int* __restrict__ rows, const 
         for (long long i = static_cast<long long>(blockIdx.x - T) * blockDim.x + threadIdx.x; i < zero_vecs;
              i += nb * blockDim.x)
             zero_ptr[i] = make_uint4(0, 0, 0, 0);
-        pdl_launch_dependents();
         return;
     }
     const int t = blockIdx.x;
@@ -77,7 +77,6 @@ rmsnorm_kernel(const float* __restrict__ x, const int* __restrict__ rows, const 
             orow[i] = o;
         }
     }
-    pdl_launch_dependents();
 }
 
 // ---- RoPE + KV page scatter (modeling_llama.py:138-168, :267) ---------------------------------------
@@ -87,6 +86,7 @@ rope_kv_write_kernel(const float* __restrict__ qkv, const int* __restrict__ posi
                      const int* __restrict__ slots, const float* __restrict__ cos_sin,
                      __nv_bfloat16* __restrict__ q_out, __nv_bfloat16* __restrict__ k_cache,
                      __nv_bfloat16* __restrict__ v_cache, int Hq, int Hkv, int D, int block_size) {
+    pdl_launch_dependents();
     pdl_wait();
     const int t = blockIdx.x;
     const int pos = positions[t];
@@ -138,12 +138,12 @@ rope_kv_write_kernel(const float* __restrict__ qkv, const int* __restrict__ posi
             *reinterpret_cast<uint2*>(v_cache + ((blk * Hkv + h) * block_size + off) * D + i) = o;
         }
     }
-    pdl_launch_dependents();
 }
 
 // ---- SwiGLU (modeling_llama.py:182-184) ----------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 silu_mul_kernel(const float4* __restrict__ gu, uint2* __restrict__ act, long long total_vec, int I4) {
+    pdl_launch_dependents();
     pdl_wait();
     for (long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; idx < total_vec;
          idx += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -156,7 +156,6 @@ silu_mul_kernel(const float4* __restrict__ gu, uint2* __restrict__ act, long lon
         o.y = pack_bf16(g.z / (1.f + expf(-g.z)) * u.z, g.w / (1.f + expf(-g.w)) * u.w);
         act[idx] = o;
     }
-    pdl_launch_dependents();
 }
 
 static void set_pdl(cudaLaunchConfig_t& cfg, cudaLaunchAttribute* attr, int flags) {

@@ -70,6 +70,7 @@ sample_kernel(const float* __restrict__ logits, long long ldl, const float* __re
               const int* __restrict__ steps, int* __restrict__ out_ids, int V) {
     __shared__ ArgMax sh_am[kSampThreads / 32];
     __shared__ float sh_f[kSampThreads / 32];
+    pdl_launch_dependents();
     pdl_wait();
     const int b = blockIdx.x;
     const float* row = logits + static_cast<long long>(b) * ldl;
