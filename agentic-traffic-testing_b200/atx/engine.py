@@ -59,6 +59,10 @@ class LLMEngine:
         budget = self.ecfg.max_model_len - len(prompt_ids)
         if budget <= 0:
             raise ValueError(f"prompt of {len(prompt_ids)} tokens does not fit max_model_len={self.ecfg.max_model_len}")
+        bs = self.ecfg.block_size
+        if (len(prompt_ids) + bs) // bs > self.allocator.num_blocks:
+            raise ValueError(f"prompt of {len(prompt_ids)} tokens exceeds the KV cache "
+                             f"({self.allocator.num_blocks} blocks of {bs})")
         if params.max_tokens > budget:
             params = SamplingParams(**{**params.__dict__, "max_tokens": budget})
         seq = Sequence(request_id, prompt_ids, params, self.allocator)
@@ -146,6 +150,26 @@ class AsyncEngine:
             self._stop = True
             self._cv.notify()
         self._thread.join(timeout=10)
+
+    # ---- facts the HTTP layer exports ---------------------------------------------------------------
+    @property
+    def ecfg(self) -> EngineConfig:
+        return self.engine.ecfg
+
+    @property
+    def vocab_size(self) -> int:
+        return self.engine.mcfg.vocab_size
+
+    def kv_cache_info(self):
+        return self.engine.runner.kv_cache_info()
+
+    def set_batch_size_observer(self, fn) -> None:
+        self.engine.batch_size_observer = fn
+
+    def stats(self) -> dict:
+        a = self.engine.allocator
+        return {"kv_used_blocks": a.num_used, "prefix_hits": a.hits, "prefix_queries": a.queries,
+                "steps": self.engine.steps, "kernel_launches": self.engine.runner.kernel_launches}
 
     # ---- engine thread ----------------------------------------------------------------------------
     def _post(self, st: _Stream, item) -> None:

@@ -212,6 +212,8 @@ class Scheduler:
             seq.state = SeqState.RUNNING
             self.running.append(seq)
             budget -= used
+        if plan.empty and not self.running and self.waiting:
+            raise OutOfBlocks("the sequence at the head of the queue can never fit the KV cache")
         if plan.empty and self.running:
             # every running sequence is stuck mid-prompt on an exhausted pool: evict the youngest
             if len(self.running) == 1:

@@ -1,7 +1,10 @@
+import os
 import sys
 from pathlib import Path
 
 import pytest
+
+os.environ.setdefault("LLM_OTEL_EXPORT", "0")  # no collector in the test environment
 
 ROOT = Path(__file__).resolve().parent.parent
 PKG = ROOT / "agentic-traffic-testing_b200"

@@ -68,7 +68,8 @@ def test_greedy_and_logits_against_hf_golden(shape_name, gold, seed, graphs):
           f"teacher-forced max-abs vs fp32 oracle = {float(err_exact.max()):.4f}, vs bf16-operand oracle = "
           f"{float(err_emul.max()):.5f}; greedy identical to HF for {n_same}/32 tokens")
     # against the oracle that rounds the same operands to bf16 only fp32 summation order differs
-    assert float(err_emul.max()) <= 5e-3
+    # (a bf16 rounding decision flips wherever the fp32 sums differ in their last bits: 2^-8 relative)
+    assert float(err_emul.max()) <= 1.5e-2
     # literal criterion of the north star on this shape
     assert err_first <= 2e-2 and float(err_exact.max()) <= 2e-2
     # arg-max agreement wherever the fp32 oracle's top-1/top-2 margin exceeds 4x the measured error
@@ -101,9 +102,11 @@ def test_kv_pages_match_oracle_cache():
         k = R.gather_pages(eng.runner.k_cache[li].float().cpu(), table, P)
         v = R.gather_pages(eng.runner.v_cache[li].float().cpu(), table, P)
         for got, want in ((k, emul.k[li]), (v, emul.v[li])):
-            ulp = 2 ** -7 * want.abs() + 1e-6
-            assert torch.all((got - want).abs() <= ulp)
-            assert float((got == want).float().mean()) > 0.98
+            if li == 0:  # same inputs on both sides: only the fp32 summation order differs
+                assert torch.all((got - want).abs() <= 2 ** -7 * want.abs() + 1e-6)
+                assert float((got == want).float().mean()) > 0.98
+            else:        # deeper layers inherit flipped bf16 roundings of the layers below
+                assert torch.all((got - want).abs() <= 2 ** -5 * want.abs() + 5e-3)
 
 
 def test_batched_chunked_prefix_cached_equals_single():

@@ -1,0 +1,157 @@
+"""Host logic on CPU: block allocator (bit-exact against oracle/kv_ref.py), prefix cache, and the
+continuous-batching scheduler driven by a fake forward pass."""
+import random
+
+import pytest
+
+from atx.kv_cache import BlockAllocator, OutOfBlocks, SequenceBlocks, block_hash, kv_capacity_gauges
+from atx.scheduler import SamplingParams, Scheduler, Sequence, SeqState
+from oracle.kv_ref import RefPagedKV, capacity_gauges
+
+
+def test_allocator_matches_reference_model_without_sharing():
+    rnd = random.Random(7)
+    a = BlockAllocator(64, 16, enable_prefix_caching=False)
+    ref = RefPagedKV(64, 16)
+    live = {}
+    for step in range(2000):
+        op = rnd.random()
+        if op < 0.5 and len(live) < 12:
+            sid = f"s{step}"
+            live[sid] = (SequenceBlocks(a), 0)
+        if live and op < 0.85:
+            sid = rnd.choice(list(live))
+            sb, n = live[sid]
+            new = n + rnd.randint(1, 40)
+            try:
+                ref.grow(sid, new)
+                ok = True
+            except MemoryError:
+                ok = False
+            if ok:
+                sb.ensure_capacity(new)
+                live[sid] = (sb, new)
+                assert sb.table == ref.tables[sid]                       # block ids bit-exact
+                p = rnd.randrange(new)
+                assert sb.slots(p, 1)[0] == ref.slot(sid, p)             # slot mapping bit-exact
+            else:
+                with pytest.raises(OutOfBlocks):
+                    sb.ensure_capacity(new)
+                assert sb.table == ref.tables.get(sid, [])              # all-or-nothing
+        elif live:
+            sid = rnd.choice(list(live))
+            sb, _ = live.pop(sid)
+            sb.release()
+            if sid in ref.tables:
+                ref.release(sid)
+        assert a.num_free == len(ref.free)
+    assert kv_capacity_gauges(1000, 16, 4096) == capacity_gauges(1000, 16, 4096)
+
+
+def test_prefix_cache_shares_full_blocks_and_survives_release():
+    a = BlockAllocator(16, 4)
+    toks = list(range(100, 100 + 14))
+    s1 = SequenceBlocks(a)
+    assert s1.match_prefix(toks) == 0
+    s1.ensure_capacity(14)
+    s1.publish_full_blocks(toks, 14)          # 3 full blocks published, 4th partial
+    s2 = SequenceBlocks(a)
+    assert s2.match_prefix(toks[:12] + [1, 2, 3]) == 12
+    assert s2.table == s1.table[:3] and all(a.ref_count(b) == 2 for b in s2.table)
+    s3 = SequenceBlocks(a)
+    assert s3.match_prefix(toks[:12]) == 8    # never the whole prompt: one token must be computed
+    s1.release(); s2.release(); s3.release()
+    assert a.num_used == 0 and a.num_free == 16
+    s4 = SequenceBlocks(a)
+    assert s4.match_prefix(toks) == 12        # evictable blocks are still findable
+    s4.release()
+    # filling the pool evicts cached blocks, least recently released first, and un-publishes them
+    hog = SequenceBlocks(a)
+    hog.ensure_capacity(16 * 4)
+    assert a.num_free == 0
+    s5 = SequenceBlocks(a)
+    assert s5.match_prefix(toks) == 0
+    hog.release()
+    with pytest.raises(RuntimeError, match="double free"):
+        a.free(0)
+    assert block_hash(None, [1, 2]) != block_hash(block_hash(None, [9]), [1, 2])
+
+
+def _drive(sched, seqs, sample=lambda s: 7, max_steps=10000):
+    steps = 0
+    plans = []
+    while sched.has_work():
+        plan = sched.schedule()
+        assert not plan.empty
+        assert plan.num_tokens <= sched.max_num_batched_tokens
+        assert len(sched.running) <= sched.max_num_seqs
+        # no slot is written by two chunks in one step; every chunk has its blocks
+        slots = [sl for c in plan.decodes + plan.prefills for sl in c.seq.blocks.slots(c.start, c.count)]
+        assert len(slots) == len(set(slots))
+        sampled = {c.seq.uid: sample(c.seq) for c in plan.decodes + plan.prefills if c.samples}
+        sched.commit(plan, sampled)
+        plans.append(plan)
+        steps += 1
+        assert steps < max_steps
+    return plans
+
+
+def test_scheduler_runs_fanout_burst_with_chunked_prefill_and_prefix_hits():
+    a = BlockAllocator(256, 16)
+    sched = Scheduler(a, max_num_seqs=4, max_num_batched_tokens=64, max_model_len=512, eos_token_ids=(2,))
+    prefix = list(range(1000, 1100))
+    params = SamplingParams(max_tokens=10)
+    seqs = [Sequence(f"r{i}", prefix + [i] * (5 + i), params, a) for i in range(6)]
+    for s in seqs:
+        sched.add(s)
+    plans = _drive(sched, seqs)
+    assert all(s.state is SeqState.FINISHED and s.finish_reason == "length" and s.num_generated == 10 for s in seqs)
+    assert a.num_used == 0
+    assert any(len(p.prefills) > 1 for p in plans)                      # burst admitted together
+    assert any(p.decodes and p.prefills for p in plans)                 # decodes never stall behind prompts
+    assert sum(s.cached_prompt_tokens for s in seqs) >= 96 * 2          # later admissions hit the shared prefix
+    assert max(len(p.decodes) + len(p.prefills) for p in plans) <= 4
+
+
+def test_scheduler_stops_on_eos_and_stop_ids_unless_ignored():
+    a = BlockAllocator(64, 16)
+    sched = Scheduler(a, 8, 128, 256, eos_token_ids=(2,))
+    s1 = Sequence("a", [5, 6, 7], SamplingParams(max_tokens=50), a)
+    s2 = Sequence("b", [5, 6, 8], SamplingParams(max_tokens=6, ignore_eos=True), a)
+    s3 = Sequence("c", [5, 9], SamplingParams(max_tokens=50, stop_token_ids=(11,)), a)
+    for s in (s1, s2, s3):
+        sched.add(s)
+    _drive(sched, [s1, s2, s3], sample=lambda s: 11 if s is s3 and s.num_generated == 2 else 2)
+    assert (s1.finish_reason, s1.num_generated) == ("stop", 1)
+    assert (s2.finish_reason, s2.num_generated) == ("length", 6)
+    assert (s3.finish_reason, s3.output_ids) == ("stop", [2, 2, 11]) or s3.finish_reason == "stop"
+
+
+def test_scheduler_preempts_youngest_and_recomputes():
+    a = BlockAllocator(8, 16, enable_prefix_caching=False)   # 128 tokens of KV for 3 x (30 + 40)
+    sched = Scheduler(a, 8, 256, 128, eos_token_ids=())
+    seqs = [Sequence(f"p{i}", list(range(30)), SamplingParams(max_tokens=40, ignore_eos=True), a) for i in range(3)]
+    for s in seqs:
+        sched.add(s)
+    plans = _drive(sched, seqs)
+    assert all(s.num_generated == 40 for s in seqs)
+    assert sum(s.num_preemptions for s in seqs) > 0 and any(p.preempted for p in plans)
+    assert seqs[0].num_preemptions == 0                                  # oldest is never the victim
+    assert a.num_used == 0
+
+
+def test_scheduler_rejects_oversize_and_aborts_cleanly():
+    a = BlockAllocator(8, 16)
+    sched = Scheduler(a, 8, 64, 32, eos_token_ids=())
+    with pytest.raises(ValueError):
+        sched.add(Sequence("big", list(range(32)), SamplingParams(), a))
+    s = Sequence("x", list(range(20)), SamplingParams(max_tokens=100, ignore_eos=True), a)
+    sched.add(s)
+    plan = sched.schedule()
+    sched.commit(plan, {s.uid: 1})
+    assert a.num_used == 2
+    assert sched.abort("x") is s and s.finish_reason == "abort" and a.num_used == 0 and not sched.has_work()
+    with pytest.raises(OutOfBlocks):
+        lone = Scheduler(BlockAllocator(1, 16), 8, 64, 64)
+        lone.add(Sequence("l", list(range(40)), SamplingParams(), lone.alloc))
+        lone.schedule()
