@@ -135,6 +135,8 @@ class ModelRunner:
         self.kernel_launches = 0  # cumulative count of our kernels launched (graph replays included)
         self.h2d_bytes = 0
         self.d2h_bytes = 0
+        # bench hook: when a list, every step appends (start_event, end_event, n_decode, prefill_tokens, ctx_sum)
+        self.step_events: Optional[list] = None
 
     # ----------------------------------------------------------------------------------------------
     def _ck(self, rc: int) -> None:
@@ -306,6 +308,10 @@ class ModelRunner:
         self._h2d_done.record()
 
         splits = self.decode_splits(B, max_len)
+        ev0 = None
+        if self.step_events is not None:
+            ev0 = torch.cuda.Event(enable_timing=True)
+            ev0.record()
         if use_graph:
             key = (B, splits)
             g = self._graphs.get(key)
@@ -316,6 +322,10 @@ class ModelRunner:
         else:
             self.launches_last_step = self._forward(T, B, splits, n_pf, max_q, n_rows)
         self.kernel_launches += self.launches_last_step
+        if ev0 is not None:
+            ev1 = torch.cuda.Event(enable_timing=True)
+            ev1.record()
+            self.step_events.append((ev0, ev1, n_dec, T_real - n_dec, sum(c.start + 1 for c in decs)))
 
         out: Dict[int, int] = {}
         if n_rows:

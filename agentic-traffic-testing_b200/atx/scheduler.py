@@ -186,6 +186,11 @@ class Scheduler:
             except OutOfBlocks:
                 return -1
             plan.prefills.append(Chunk(seq, seq.num_computed, count, count == remaining))
+            # Publish the blocks this chunk will fill BEFORE the forward pass: requests admitted later
+            # in this same step (a fan-out burst arrives together) attach to them instead of
+            # recomputing the shared prefix. Safe because the K/V writes of every token in the batch
+            # precede the attention reads of that layer, and nothing is preempted after this point.
+            seq.blocks.publish_full_blocks(seq.tokens, seq.num_computed + count)
             return count
 
         for seq in self.running:

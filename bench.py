@@ -1,0 +1,418 @@
+#!/usr/bin/env python3
+"""Headline benchmark: Llama-3.1-8B agent fan-out burst on B200 (BASELINE.json configs[1]).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+One "step" = one fan-out job: 1 orchestrator + 5 worker requests arriving together (batch 6), each a
+1024-token prompt (768-token shared prefix + 256 unique tokens, fresh ids every step so nothing is
+cached across steps), 256 greedy output tokens each with EOS ignored -> 1536 output tokens per step.
+Prints ONE JSON line (rank 0): decode tokens/s (`value`, device-timed whole-job throughput through the
+engine), p50 TTFT, `e2e` (same job through the drop-in HTTP API /chat with host text prompts),
+`roofline` of the dominant kernel (the tcgen05 weight-streaming GEMM), the whole-decode-step HBM
+fraction, `cpu_baseline` (the reference's CPU arithmetic, HF LlamaForCausalLM fp32, bounded sample).
+With N > 1 (torchrun) every rank serves its own replica of the same burst (weak scaling, no
+data-path collective); times are max over ranks.
+"""
+from __future__ import annotations
+
+import argparse
+import asyncio
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT / "agentic-traffic-testing_b200"))
+sys.path.insert(0, str(ROOT))
+os.environ.setdefault("LLM_OTEL_EXPORT", "0")
+os.environ.setdefault("LLM_IGNORE_EOS", "1")
+
+METRIC = "Llama-3.1-8B decode tokens/s + p50 TTFT under agent fan-out"
+UNIT = "tokens/s"
+BATCH, PROMPT, SHARED, OUT = 6, 1024, 768, 256
+
+
+def peaks() -> dict:
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        d = json.loads(p.read_text())
+        return {"hbm_gbs": float(d["hbm_gbs"]), "source": "measured (MEASURED_PEAKS.json)"}
+    return {"hbm_gbs": 6650.0, "source": "fallback (B200_PROFILING.md)"}
+
+
+def burst_prompts(step: int, vocab: int = 128000):
+    """Token ids of one fan-out burst: shared prefix + unique suffixes; seed depends on the step."""
+    import numpy as np
+
+    rng = np.random.default_rng(2 + 1000 * step)
+    shared = rng.integers(0, vocab, SHARED).tolist()
+    return [shared + rng.integers(0, vocab, PROMPT - SHARED).tolist() for _ in range(BATCH)]
+
+
+def burst_texts(step: int):
+    """Same burst shape as text for the HTTP arm: the offline byte tokenizer maps 1 ASCII char to 1
+    token, so a 1024-char prompt is a 1024-token prompt."""
+    import numpy as np
+
+    rng = np.random.default_rng(7 + 1000 * step)
+    alphabet = np.frombuffer(b"abcdefghijklmnopqrstuvwxyz ABCDEFGHIJKLMNOPQRSTUVWXYZ0123456789.,", dtype=np.uint8)
+    shared = bytes(rng.choice(alphabet, SHARED)).decode()
+    return [shared + bytes(rng.choice(alphabet, PROMPT - SHARED)).decode() for _ in range(BATCH)]
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons of one GPU every 200 ms while the timed region runs."""
+
+    def __init__(self, index: int):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz, self._stop_ev = index, [], set(), None, threading.Event()
+
+    def run(self):
+        try:
+            import pynvml as nv
+
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+            names = {getattr(nv, k): k for k in dir(nv) if k.startswith("nvmlClocksThrottleReason")
+                     or k.startswith("nvmlClocksEventReason")}
+            while not self._stop_ev.is_set():
+                self.samples.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                try:
+                    bits = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                    for bit, name in names.items():
+                        if isinstance(bit, int) and bit and bits & bit and "None" not in name and "All" not in name:
+                            self.reasons.add(name.replace("nvmlClocksThrottleReason", "").replace(
+                                "nvmlClocksEventReason", ""))
+                except Exception:
+                    pass
+                self._stop_ev.wait(0.2)
+        except Exception as exc:  # NVML missing: say so in the record rather than inventing clocks
+            self.reasons.add(f"nvml_unavailable:{type(exc).__name__}")
+
+    def finish(self) -> dict:
+        self._stop_ev.set()
+        self.join(timeout=2)
+        rs = sorted({r[0].lower() + r[1:] for r in self.reasons})
+        return {"sm_mhz": statistics.median(self.samples) if self.samples else None, "sm_max_mhz": self.max_mhz,
+                "reasons": rs, "samples": len(self.samples)}
+
+
+# ------------------------------------------------------------------------------------------------------
+def run_burst(engine, prompts):
+    """Submit the burst and step the engine to completion. Returns the finished sequences."""
+    from atx.scheduler import SamplingParams
+
+    params = SamplingParams(temperature=0.0, max_tokens=OUT, ignore_eos=True)
+    t = time.monotonic()
+    seqs = [engine.add_request(f"b{time.monotonic_ns()}-{i}", p, params) for i, p in enumerate(prompts)]
+    for s in seqs:
+        s.arrival = t
+    while engine.has_work():
+        engine.step()
+    return seqs
+
+
+async def http_bursts(app, steps, first_step, record):
+    """K bursts through POST /chat on a real localhost socket, 6 concurrent clients per burst."""
+    import aiohttp
+    from aiohttp import web
+
+    runner = web.AppRunner(app)
+    await runner.setup()
+    site = web.TCPSite(runner, "127.0.0.1", 0)
+    await site.start()
+    port = site._server.sockets[0].getsockname()[1]
+    url = f"http://127.0.0.1:{port}/chat"
+    async with aiohttp.ClientSession(timeout=aiohttp.ClientTimeout(total=600)) as sess:
+        async def one(text):
+            async with sess.post(url, json={"prompt": text, "max_tokens": OUT, "skip_chat_template": True}) as r:
+                body = await r.json()
+                assert r.status == 200, body
+                return body["meta"]
+        for k in range(steps):
+            metas = await asyncio.gather(*[one(t) for t in burst_texts(first_step + k)])
+            record(metas)
+    await runner.cleanup()
+
+
+def gemm_roofline(engine, T: int, hbm_gbs: float) -> dict:
+    """Dominant kernel timed live: every GEMM launch of one decode step (4 per layer + LM head, the
+    engine's own weights, so 15 GB are streamed and L2 never helps), CUDA events on the launch stream."""
+    import torch
+
+    from atx import _cabi
+
+    r, m = engine.runner, engine.mcfg
+    lib, st = r.lib, r.stream
+    H, I, V = m.hidden_size, m.intermediate_size, m.vocab_size
+
+    def one_pass():
+        s = st.cuda_stream
+        for p_qkv, p_o, p_gu, p_down in r.plans:
+            lib.atx_gemm_run(p_qkv._h, r.qkv.data_ptr(), m.qkv_size, T, 1, 0, r.flags, s)
+            lib.atx_gemm_run(p_o._h, r.h.data_ptr(), H, T, 1, 0, r.flags, s)
+            lib.atx_gemm_run(p_gu._h, r.gu.data_ptr(), 2 * I, T, 1, 0, r.flags, s)
+            lib.atx_gemm_run(p_down._h, r.h.data_ptr(), H, T, 1, 0, r.flags, s)
+        lib.atx_gemm_run(r.plan_lm._h, r.logits.data_ptr(), V, T, 0, 1, r.flags, s)
+
+    with torch.cuda.stream(st):
+        for _ in range(3):
+            one_pass()
+        st.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        iters = 10
+        e0.record(st)
+        for _ in range(iters):
+            one_pass()
+        e1.record(st)
+        st.synchronize()
+    launches = 4 * m.num_hidden_layers + 1
+    ms = e0.elapsed_time(e1) / iters
+    act = T * 2 * (m.num_hidden_layers * (2 * H + m.q_size + I) + H)           # bf16 activations read
+    outb = T * 4 * (m.num_hidden_layers * (m.qkv_size + 2 * H + 2 * I) + V)    # fp32 results written
+    byts = m.weight_bytes_per_decode_step() + act + outb
+    achieved = byts / ms / 1e6
+    traffic = None
+    tp = ROOT / "profiles" / "gemm_traffic.json"
+    if tp.exists():
+        traffic = json.loads(tp.read_text()).get("dram_bytes_per_launch")
+    return {"bound": "hbm", "kernel": "gemm_wt_kernel<16> (tcgen05 weight-streaming GEMM, decode T=%d)" % T,
+            "achieved": round(achieved, 1), "peak": hbm_gbs, "unit": "GB/s", "frac": round(achieved / hbm_gbs, 4),
+            "traffic": traffic, "bytes_per_launch": round(byts / launches), "us_per_launch": round(1e3 * ms / launches, 3),
+            "launches_per_decode_step": launches}
+
+
+def cpu_reference_sample(threads: int, prompt_len: int = 64, new_tokens: int = 4, layers: int = 32):
+    """The reference's CPU path (llm/hf_cpu_server.py:39-50,91): transformers LlamaForCausalLM, fp32,
+    device=cpu, on a bounded sample of the burst (same model shape and batch; shorter prompt, fewer
+    new tokens). Greedy instead of the reference's temperature=0.7 sampling: same arithmetic per token."""
+    import torch
+    from transformers import LlamaConfig, LlamaForCausalLM
+
+    torch.set_num_threads(threads)
+    cfg = LlamaConfig(vocab_size=128256, hidden_size=4096, intermediate_size=14336, num_hidden_layers=layers,
+                      num_attention_heads=32, num_key_value_heads=8, head_dim=128, rms_norm_eps=1e-5,
+                      rope_theta=500000.0, max_position_embeddings=131072, tie_word_embeddings=False,
+                      rope_scaling={"rope_type": "llama3", "factor": 8.0, "low_freq_factor": 1.0,
+                                    "high_freq_factor": 4.0, "original_max_position_embeddings": 8192})
+    t0 = time.perf_counter()
+    with torch.device("meta"):
+        model = LlamaForCausalLM(cfg)
+    model = model.to_empty(device="cpu").to(torch.float32)
+    tile = torch.randn(1 << 20) * 0.02
+    for name, p in model.named_parameters():  # cheap random fill: values do not affect CPU speed
+        flat = p.data.view(-1)
+        if p.dim() == 1:
+            flat.fill_(1.0)
+            continue
+        k = tile.numel()
+        n = flat.numel() // k * k
+        flat[:n].view(-1, k).copy_(tile)
+        flat[n:].copy_(tile[: flat.numel() - n])
+    from transformers.models.llama.modeling_llama import LlamaRotaryEmbedding
+
+    model.model.rotary_emb = LlamaRotaryEmbedding(config=cfg, device="cpu")
+    model.eval()
+    init_s = time.perf_counter() - t0
+    g = torch.Generator().manual_seed(2)
+    ids = torch.randint(0, 128000, (BATCH, prompt_len), generator=g)
+    with torch.no_grad():
+        t1 = time.perf_counter()
+        out = model(ids, use_cache=True)
+        t2 = time.perf_counter()
+        past, nxt = out.past_key_values, out.logits[:, -1].argmax(-1, keepdim=True)
+        for _ in range(new_tokens):
+            out = model(nxt, past_key_values=past, use_cache=True)
+            past, nxt = out.past_key_values, out.logits[:, -1].argmax(-1, keepdim=True)
+        t3 = time.perf_counter()
+    prefill_s, decode_s = t2 - t1, t3 - t2
+    per_step = decode_s / new_tokens
+    est_full = prefill_s * (PROMPT / prompt_len) + per_step * OUT  # GEMM-dominated: linear in tokens
+    return {"value": round(BATCH * new_tokens / (prefill_s + decode_s), 3), "unit": UNIT, "cores": threads,
+            "kind": "reference",
+            "sample": (f"transformers.LlamaForCausalLM fp32 on CPU (the class llm/hf_cpu_server.py:39-50 loads), "
+                       f"8B shape x {layers} layers, batch {BATCH}, {prompt_len}-token prompts, {new_tokens} greedy "
+                       f"tokens; prefill {prefill_s:.2f}s, decode {per_step:.3f}s/step, init {init_s:.0f}s"),
+            "decode_only_tokens_per_s": round(BATCH / per_step, 3),
+            "extrapolated_full_workload_tokens_per_s": round(BATCH * OUT / est_full, 3),
+            "extrapolated_full_workload_ttft_s": round(prefill_s * (PROMPT / prompt_len), 2)}
+
+
+# ------------------------------------------------------------------------------------------------------
+def main() -> None:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--model", default="8b")
+    ap.add_argument("--no-prefix-cache", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    threads = os.cpu_count() or 1
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        samples = [cpu_reference_sample(threads) for _ in range(max(1, min(args.steps, 2)))]
+        best = max(samples, key=lambda s: s["value"])
+        print(json.dumps({
+            "impl": "reference", "metric": METRIC, "value": best["value"], "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": None, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "configs[1] fan-out burst, bounded CPU sample (see cpu_baseline.sample)"},
+            "cpu_baseline": best,
+            "e2e": {"value": best["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        }))
+        return
+
+    import torch
+
+    from atx.config import EngineConfig, ModelSource, model_config_by_name
+    from atx.engine import AsyncEngine, LLMEngine
+
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    mcfg = model_config_by_name(args.model)
+    ecfg = EngineConfig(max_model_len=4096, max_num_seqs=12, max_num_batched_tokens=8192,
+                        gpu_memory_utilization=0.90, enable_prefix_caching=not args.no_prefix_cache, device=local)
+    engine = LLMEngine(ModelSource(mcfg, None, 0), ecfg)
+    r = engine.runner
+    pk = peaks()
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for w in range(args.warmup):  # also captures the decode CUDA graphs for every KV-split bucket
+        run_burst(engine, burst_prompts(-1 - w))
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    l0, h0, d0, s0 = r.kernel_launches, r.h2d_bytes, r.d2h_bytes, engine.steps
+    r.step_events = []  # (start, end, n_decode, n_prefill_tokens, ctx_sum) per engine step
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ttfts = []
+    e0.record(r.stream)
+    t_host0 = time.perf_counter()
+    for k in range(args.steps):
+        seqs = run_burst(engine, burst_prompts(k))
+        ttfts += [s.first_token_time - s.arrival for s in seqs]
+        assert all(s.num_generated == OUT for s in seqs)
+    e1.record(r.stream)
+    barrier()
+    host_ms = (time.perf_counter() - t_host0) * 1e3
+    clocks = sampler.finish()
+    dev_ms = e0.elapsed_time(e1)
+    launches = r.kernel_launches - l0
+    eng_steps = engine.steps - s0
+    step_events, r.step_events = r.step_events, None
+    t = torch.tensor([dev_ms, host_ms], device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        all_ttft = [None] * world
+        dist.all_gather_object(all_ttft, ttfts)
+        ttfts = [x for part in all_ttft for x in part]
+    dev_ms = float(t[0])
+    tokens = args.steps * BATCH * OUT * world
+    value = tokens / (dev_ms / 1e3)
+
+    # ---- whole decode step against the HBM roofline (events recorded inside the timed region) ----
+    dec = [(s.elapsed_time(e), nd, ctx) for (s, e, nd, npf, ctx) in step_events if npf == 0 and nd == BATCH]
+    decode_step = None
+    if dec:
+        ms = sum(d[0] for d in dec) / len(dec)
+        byts = mcfg.weight_bytes_per_decode_step() + mcfg.kv_bytes_per_token() * (sum(d[2] for d in dec) / len(dec))
+        decode_step = {"ms": round(ms, 4), "algorithmic_bytes": round(byts), "achieved": round(byts / ms / 1e6, 1),
+                       "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": round(byts / ms / 1e6 / pk["hbm_gbs"], 4),
+                       "steps_measured": len(dec), "decode_tokens_per_s": round(BATCH / ms * 1e3, 1)}
+    pf = [(s.elapsed_time(e), npf) for (s, e, nd, npf, ctx) in step_events if npf > 0]
+    prefill = {"ms_per_burst": round(sum(p[0] for p in pf) / args.steps, 3),
+               "tokens_computed_per_burst": round(sum(p[1] for p in pf) / args.steps)} if pf else None
+
+    roof = gemm_roofline(engine, BATCH, pk["hbm_gbs"])
+    roof["peak_source"] = pk["source"]
+
+    # ---- end to end through the drop-in HTTP API (host text in, text out) -------------------------
+    e2e = None
+    if not args.no_e2e:
+        from llm import serve_llm as S
+        from llm.backend import B200Backend
+
+        aeng = AsyncEngine(engine)
+        S._backend = B200Backend("random:%s" % args.model, ecfg.max_model_len, None, ecfg.max_num_seqs,
+                                 ecfg.max_num_batched_tokens, ecfg.gpu_memory_utilization, tracer=S._tracer,
+                                 engine=aeng)
+        metas = []
+        import contextlib
+        import io
+
+        quiet = io.StringIO()
+        with contextlib.redirect_stdout(quiet):  # the server logs one line per request event
+            asyncio.run(http_bursts(S.create_app(), 1, 10_000, lambda m: None))  # warm the HTTP path
+            barrier()
+            h0, d0 = r.h2d_bytes, r.d2h_bytes
+            tw = time.perf_counter()
+            asyncio.run(http_bursts(S.create_app(), args.steps, 20_000, metas.append))
+            barrier()
+            wall = time.perf_counter() - tw
+        aeng.shutdown()
+        tw_t = torch.tensor([wall], device="cuda")
+        if dist is not None:
+            dist.all_reduce(tw_t, op=dist.ReduceOp.MAX)
+        flat = [m for burst in metas for m in burst]
+        assert all(m["completion_tokens"] == OUT and m["prompt_tokens"] == PROMPT for m in flat)
+        e2e = {"value": round(tokens / float(tw_t[0]), 1), "unit": UNIT,
+               "h2d_bytes_per_step": round((r.h2d_bytes - h0) / args.steps),
+               "d2h_bytes_per_step": round((r.d2h_bytes - d0) / args.steps),
+               "ttft_p50_ms": round(1e3 * statistics.median(m["queue_wait_s"] for m in flat), 2),
+               "path": "HTTP POST /chat on 127.0.0.1 (aiohttp server + client), text prompts, byte tokenizer"}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        try:
+            cpu = cpu_reference_sample(threads)
+        except Exception as exc:  # e.g. not enough host RAM for 32 GB of fp32 weights
+            cpu = {"value": None, "unit": UNIT, "cores": threads, "kind": "reference",
+                   "sample": f"failed: {type(exc).__name__}: {exc}"}
+
+    if rank == 0:
+        print(json.dumps({
+            "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": round(dev_ms / args.steps, 3), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": "BASELINE configs[1]: Llama-3.1-8B (32 layers, random init seed 0) on 1xB200 per "
+                                   "replica; agent-a + 5 agent-b fan-out burst = batch 6, 1024-token prompts "
+                                   "(768 shared + 256 unique, fresh ids each step), 256 greedy tokens each",
+                       "parallelism": f"dp{world} (independent replicas, no collective)",
+                       "prefix_cache": not args.no_prefix_cache, "cuda_graphs": True, "pdl": bool(r.flags),
+                       "l2": "inputs larger than L2: 15 GB of weights streamed per decode step vs 126 MB L2",
+                       "max_num_seqs": ecfg.max_num_seqs, "max_num_batched_tokens": ecfg.max_num_batched_tokens,
+                       "kv_blocks": r.num_blocks},
+            "ttft_p50_ms": round(1e3 * statistics.median(ttfts), 2),
+            "ttft_max_ms": round(1e3 * max(ttfts), 2),
+            "host_ms_per_step": round(float(t[1]) / args.steps, 3),
+            "gpu_launches": launches, "engine_steps": eng_steps,
+            "clocks": clocks, "roofline": roof, "decode_step": decode_step, "prefill": prefill, "e2e": e2e,
+            "cpu_baseline": cpu,
+        }))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

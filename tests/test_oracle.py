@@ -83,7 +83,7 @@ def test_attention_restatement_edge_cases():
 def test_sampler_restatement():
     logits = np.array([0.1, 3.0, 3.0, -1.0], dtype=np.float32)
     assert SR.sample(logits, 0.0, 1.0, 1, 0) == 1  # first maximum
-    keep = SR.nucleus_mask(np.log(np.array([0.5, 0.3, 0.15, 0.05])), 1.0, 0.8)
+    keep = SR.nucleus_mask(np.log(np.array([0.5, 0.3, 0.15, 0.05])), 1.0, 0.79)
     assert keep.tolist() == [True, True, False, False]
     keep = SR.nucleus_mask(np.log(np.array([0.5, 0.3, 0.15, 0.05])), 1.0, 0.81)
     assert keep.tolist() == [True, True, True, False]
