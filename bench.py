@@ -48,7 +48,7 @@ def burst_prompts(step: int, vocab: int = 128000):
     """Token ids of one fan-out burst: shared prefix + unique suffixes; seed depends on the step."""
     import numpy as np
 
-    rng = np.random.default_rng(2 + 1000 * step)
+    rng = np.random.default_rng(2 + 1000 * (step + 1000))
     shared = rng.integers(0, vocab, SHARED).tolist()
     return [shared + rng.integers(0, vocab, PROMPT - SHARED).tolist() for _ in range(BATCH)]
 
@@ -58,7 +58,7 @@ def burst_texts(step: int):
     token, so a 1024-char prompt is a 1024-token prompt."""
     import numpy as np
 
-    rng = np.random.default_rng(7 + 1000 * step)
+    rng = np.random.default_rng(7 + 1000 * (step + 1000))
     alphabet = np.frombuffer(b"abcdefghijklmnopqrstuvwxyz ABCDEFGHIJKLMNOPQRSTUVWXYZ0123456789.,", dtype=np.uint8)
     shared = bytes(rng.choice(alphabet, SHARED)).decode()
     return [shared + bytes(rng.choice(alphabet, PROMPT - SHARED)).decode() for _ in range(BATCH)]
