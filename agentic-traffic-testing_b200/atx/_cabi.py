@@ -18,11 +18,13 @@ _LIB_PATH = _PKG_ROOT / "lib" / "libatx_b200.so"
 GEMM_STORE_F32 = 0
 GEMM_ADD_F32 = 1
 GEMM_STORE_BF16 = 2
+GEMM_SWIGLU_BF16 = 3
 FLAG_PDL = 1
 
 EXPORTS = [
     "atx_last_error", "atx_version", "atx_device_info",
     "atx_gemm_plan_create", "atx_gemm_plan_destroy", "atx_gemm_run", "atx_gemm_auto_splits",
+    "atx_gemm_set_l2_prefetch",
     "atx_embed_gather", "atx_rmsnorm", "atx_rope_kv_write", "atx_silu_mul",
     "atx_paged_attn_decode_workspace_bytes", "atx_paged_attn_decode", "atx_paged_attn_prefill",
     "atx_sample",
@@ -66,6 +68,8 @@ def load() -> C.CDLL:
     lib.atx_gemm_plan_destroy.restype = None
     lib.atx_gemm_run.argtypes = [vp, vp, i64, i32, i32, i32, i32, vp]
     lib.atx_gemm_auto_splits.argtypes = [i64, i64, i32]
+    lib.atx_gemm_set_l2_prefetch.argtypes = [i32]
+    lib.atx_gemm_set_l2_prefetch.restype = None
     lib.atx_embed_gather.argtypes = [vp, vp, vp, i32, i32, i32, vp]
     lib.atx_rmsnorm.argtypes = [vp, vp, vp, vp, i32, i32, f32, vp, i64, i32, vp]
     lib.atx_rope_kv_write.argtypes = [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp]
@@ -119,8 +123,9 @@ class GemmPlan:
 
     def run(self, out: torch.Tensor, T: int, mode: int, splits: int = 0, flags: int = 0) -> None:
         _dev(out)
-        want = torch.bfloat16 if mode == GEMM_STORE_BF16 else torch.float32
-        assert out.dtype == want and out.dim() == 2 and out.shape[1] >= self.N and out.shape[0] >= T
+        want = torch.bfloat16 if mode in (GEMM_STORE_BF16, GEMM_SWIGLU_BF16) else torch.float32
+        cols = self.N // 2 if mode == GEMM_SWIGLU_BF16 else self.N
+        assert out.dtype == want and out.dim() == 2 and out.shape[1] >= cols and out.shape[0] >= T
         _check(load().atx_gemm_run(self._h, out.data_ptr(), out.stride(0), T, mode, splits, flags, _stream()))
 
     def __del__(self):

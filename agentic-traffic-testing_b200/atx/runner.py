@@ -15,12 +15,13 @@ Layer schedule (per token batch of T rows; h is the fp32 residual stream):
   q, K/V pages = rope(qkv)   -> bf16      (scatter by slot mapping)
   a = paged attention        -> bf16
   h += a @ Wo^T                            (GEMM epilogue adds into the residual)
-  xn = rmsnorm(h); gu = xn @ Wgu^T; act = silu(g) * u; h += act @ Wdown^T
+  xn = rmsnorm(h); act = swiglu(xn @ Wgu^T) (GEMM epilogue, bf16); h += act @ Wdown^T
 """
 from __future__ import annotations
 
 import ctypes as C
 import math
+import os
 from typing import Dict, List, Optional, Tuple
 
 import numpy as np
@@ -63,7 +64,6 @@ class ModelRunner:
         self.qkv = torch.zeros(T, m.qkv_size, dtype=f32, device=dev)
         self.q = torch.zeros(T, m.q_size, dtype=bf, device=dev)
         self.attn = torch.zeros(T, m.q_size, dtype=bf, device=dev)
-        self.gu = torch.zeros(T, 2 * I, dtype=f32, device=dev)
         self.act = torch.zeros(T, I, dtype=bf, device=dev)
         self.xl = torch.zeros(S, H, dtype=bf, device=dev)
         self.logits = torch.zeros(S, V, dtype=f32, device=dev)
@@ -130,6 +130,7 @@ class ModelRunner:
         self.stream = torch.cuda.Stream(device=dev)   # every launch and copy of this runner
         self._h2d_done = torch.cuda.Event()
         self.flags = _cabi.FLAG_PDL if e.use_pdl else 0
+        self.lib.atx_gemm_set_l2_prefetch(int(os.environ.get("ATX_L2_PREFETCH_KB", "16")))
         self.scale = float(m.head_dim) ** -0.5
         self.launches_last_step = 0
         self.kernel_launches = 0  # cumulative count of our kernels launched (graph replays included)
@@ -151,13 +152,11 @@ class ModelRunner:
         H, I, V = m.hidden_size, m.intermediate_size, m.vocab_size
         Hq, Hkv, D = m.num_attention_heads, m.num_key_value_heads, m.head_dim
         dp = self._dp
-        h, xn, qkv, q, attn, gu, act = (t.data_ptr() for t in (self.h, self.xn, self.qkv, self.q, self.attn,
-                                                                self.gu, self.act))
+        h, xn, qkv, q, attn, act = (t.data_ptr() for t in (self.h, self.xn, self.qkv, self.q, self.attn, self.act))
         n = 0
         ck(lib.atx_embed_gather(dp["ids"], w.embed.data_ptr(), h, T, H, V, st))
         n += 1
         sp_qkv = lib.atx_gemm_auto_splits(m.qkv_size, H, T)
-        sp_gu = lib.atx_gemm_auto_splits(2 * I, H, T)
         qb = m.q_size * 2  # bytes per row of q / attn
         for li, l in enumerate(w.layers):
             p_qkv, p_o, p_gu, p_down = self.plans[li]
@@ -182,15 +181,10 @@ class ModelRunner:
                                               self.scale, fl, st))
                 n += 1
             ck(lib.atx_gemm_run(p_o._h, h, H, T, _cabi.GEMM_ADD_F32, 0, fl, st))
-            if sp_gu > 1:
-                ck(lib.atx_rmsnorm(h, None, l.ln2.data_ptr(), xn, T, H, m.rms_norm_eps, gu, T * 2 * I * 4, fl, st))
-                ck(lib.atx_gemm_run(p_gu._h, gu, 2 * I, T, _cabi.GEMM_ADD_F32, sp_gu, fl, st))
-            else:
-                ck(lib.atx_rmsnorm(h, None, l.ln2.data_ptr(), xn, T, H, m.rms_norm_eps, None, 0, fl, st))
-                ck(lib.atx_gemm_run(p_gu._h, gu, 2 * I, T, _cabi.GEMM_STORE_F32, 1, fl, st))
-            ck(lib.atx_silu_mul(gu, act, T, I, fl, st))
+            ck(lib.atx_rmsnorm(h, None, l.ln2.data_ptr(), xn, T, H, m.rms_norm_eps, None, 0, fl, st))
+            ck(lib.atx_gemm_run(p_gu._h, act, I, T, _cabi.GEMM_SWIGLU_BF16, 1, fl, st))  # silu(g)*u in the epilogue
             ck(lib.atx_gemm_run(p_down._h, h, H, T, _cabi.GEMM_ADD_F32, 0, fl, st))
-            n += 5
+            n += 4
         if n_rows:
             ck(lib.atx_rmsnorm(h, dp["rows"], w.norm.data_ptr(), self.xl.data_ptr(), n_rows, H, m.rms_norm_eps, None,
                                0, fl, st))
@@ -207,13 +201,15 @@ class ModelRunner:
         self.h2d_bytes += 4 * count
 
     def decode_splits(self, n_dec: int, max_len: int) -> int:
-        """KV partitions per sequence: enough CTAs to cover the SMs, >= 256 tokens per partition."""
+        """KV partitions per sequence. Short-context decode attention is a latency chain (block table
+        -> K/V rows -> softmax), so cut it short: ~64 tokens per CTA while the grid stays within a
+        few waves (<= 16 CTAs of 128 threads per SM), power-of-two buckets for the graph cache."""
         if n_dec == 0:
             return 1
-        want = max(1, (2 * 148) // max(1, n_dec * self.m.num_key_value_heads))
-        by_len = max(1, max_len // 256)
+        by_len = max(1, (max_len + 63) // 64)
+        by_grid = max(1, (16 * 148) // max(1, n_dec * self.m.num_key_value_heads))
         s = 1
-        while s * 2 <= min(want, by_len, self.max_splits):
+        while s * 2 <= min(by_len, by_grid, self.max_splits):
             s *= 2
         return s
 

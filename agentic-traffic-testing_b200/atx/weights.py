@@ -3,7 +3,9 @@
 HF state-dict names (transformers LlamaForCausalLM) are fused per layer into
   wqkv  [(Hq + 2 Hkv) * D, H]   = cat(q_proj, k_proj, v_proj)      one GEMM, one pass over x
   wo    [H, Hq * D]
-  wgu   [2 I, H]                = cat(gate_proj, up_proj)           one GEMM
+  wgu   [2 I, H]                = gate_proj / up_proj rows INTERLEAVED in groups of 64, so one GEMM
+                                  tile holds 64 gate + the 64 matching up features and the
+                                  SwiGLU runs in the GEMM epilogue (ATX_GEMM_SWIGLU_BF16)
   wdown [H, I]
 all bf16 row-major [out_features, in_features] (the layout torch.nn.Linear / HF store, K-major for
 the tcgen05 GEMM, so no transposition ever happens).
@@ -16,6 +18,14 @@ from typing import Dict, List, Optional
 import torch
 
 from .config import ModelConfig
+
+
+def interleave_gate_up(gate: torch.Tensor, up: torch.Tensor) -> torch.Tensor:
+    """[I, H] x 2 -> [2I, H]: rows [128j, 128j+64) = gate[64j:64j+64], rows [128j+64, 128j+128) = up[64j:...]."""
+    I, H = gate.shape
+    if I % 64:
+        raise ValueError("intermediate_size must be a multiple of 64")
+    return torch.stack((gate.reshape(I // 64, 64, H), up.reshape(I // 64, 64, H)), dim=1).reshape(2 * I, H)
 
 
 class LayerWeights:
@@ -67,7 +77,7 @@ class ModelWeights:
                                     sd[p + "self_attn.v_proj.weight"]], dim=0))
             l.wo = dev(sd[p + "self_attn.o_proj.weight"])
             l.ln2 = dev(sd[p + "post_attention_layernorm.weight"])
-            l.wgu = dev(torch.cat([sd[p + "mlp.gate_proj.weight"], sd[p + "mlp.up_proj.weight"]], dim=0))
+            l.wgu = dev(interleave_gate_up(sd[p + "mlp.gate_proj.weight"], sd[p + "mlp.up_proj.weight"]))
             l.wdown = dev(sd[p + "mlp.down_proj.weight"])
             w.layers.append(l)
         w.norm = dev(sd["model.norm.weight"])

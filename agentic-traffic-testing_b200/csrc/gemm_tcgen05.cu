@@ -43,7 +43,7 @@ template <int TN>
 __global__ void __launch_bounds__(kGemmThreads)
 gemm_wt_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmX,
                void* __restrict__ out, long long ldo, int T, int N, int kb_total, int kb_per_split,
-               int mode, int w_evict_first) {
+               int mode, int w_evict_first, int l2_prefetch_kb) {
     using Cfg = GemmCfg<TN>;
     extern __shared__ uint8_t smem_raw[];
     // SWIZZLE_128B tiles must sit on 1024-byte boundaries
@@ -95,6 +95,9 @@ gemm_wt_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
                     tma_load_2d(smem + i * Cfg::kStageBytes, &tmW, &full_bar[i],
                                 (kb_begin + i) * kBK, n0, polW);
                 }
+                // ... and the next slices go to L2, so HBM keeps streaming through the dependency gap
+                const int ahead = min(nkb, pre + l2_prefetch_kb);
+                for (int i = pre; i < ahead; ++i) tma_prefetch_l2_2d(&tmW, (kb_begin + i) * kBK, n0);
                 pdl_wait();
                 for (int i = 0; i < pre; ++i) {
                     tma_load_2d(smem + i * Cfg::kStageBytes + Cfg::kStageBytesW, &tmX, &full_bar[i],
@@ -150,6 +153,44 @@ gemm_wt_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
         mbar_wait(accum_bar, 0);
         tc_fence_after();
         pdl_wait();  // `out` may be the residual stream written by the upstream grid
+        if (mode == ATX_GEMM_SWIGLU_BF16) {
+            // Rows [0,64) of this tile are gate features, rows [64,128) the matching up features
+            // (weights interleaved in 64-row groups at load time): act = silu(gate) * up, bf16.
+            // The up half crosses from warps 2-3 to warps 0-1 through the (now idle) stage buffers.
+            float* su = reinterpret_cast<float*>(smem);  // [TN][64]
+            if (warp >= 2) {
+#pragma unroll 1
+                for (int c = 0; c < TN; c += 16) {
+                    if (t0 + c >= T) break;
+                    uint32_t v[16];
+                    tmem_ld16(tmem_acc + (static_cast<uint32_t>(warp * 32) << 16) + c, v);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) su[(c + j) * 64 + (warp - 2) * 32 + lane] = __uint_as_float(v[j]);
+                }
+            }
+            __syncthreads();
+            if (warp < 2) {
+                const int i = warp * 32 + lane;                 // feature within the 64-group
+                const long long col = static_cast<long long>(blockIdx.x) * 64 + i;
+                const bool ok = col < N / 2;
+                __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out);
+#pragma unroll 1
+                for (int c = 0; c < TN; c += 16) {
+                    if (t0 + c >= T) break;
+                    uint32_t v[16];
+                    tmem_ld16(tmem_acc + (static_cast<uint32_t>(warp * 32) << 16) + c, v);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        const int t = t0 + c + j;
+                        const float g = __uint_as_float(v[j]);
+                        const float a = g / (1.f + expf(-g)) * su[(c + j) * 64 + i];
+                        if (ok && t < T) o[static_cast<long long>(t) * ldo + col] = __float2bfloat16_rn(a);
+                    }
+                }
+            }
+        } else {
         const int n = n0 + warp * 32 + lane;
         const bool n_ok = n < N;
 #pragma unroll 1
@@ -183,6 +224,7 @@ gemm_wt_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
                     }
                 }
             }
+        }
         }
     }
     tc_fence_before();
@@ -246,6 +288,9 @@ struct atx_gemm_plan {
 
 using namespace atx;
 
+// k-blocks (16 KB each) of weights a CTA prefetches into L2 before it waits for the upstream grid
+static int g_l2_prefetch_kb = 16;
+
 template <int TN>
 static int launch_gemm(const atx_gemm_plan* p, int ti, void* out, long long ldo, int T, int mode,
                        int splits, int pdl, cudaStream_t stream) {
@@ -273,7 +318,8 @@ static int launch_gemm(const atx_gemm_plan* p, int ti, void* out, long long ldo,
     cfg.attrs = attr;
     cfg.numAttrs = pdl ? 1 : 0;
     ATX_CUDA(cudaLaunchKernelEx(&cfg, gemm_wt_kernel<TN>, p->tmW, p->tmX[ti], out, ldo, T,
-                                static_cast<int>(p->N), kb_total, kb_per, mode, p->w_evict_first));
+                                static_cast<int>(p->N), kb_total, kb_per, mode, p->w_evict_first,
+                                pdl ? g_l2_prefetch_kb : 0));
     return ATX_OK;
 }
 
@@ -306,16 +352,22 @@ int atx_gemm_plan_create(atx_gemm_plan** plan, const void* W, long long N, long 
 
 void atx_gemm_plan_destroy(atx_gemm_plan* plan) { delete plan; }
 
+void atx_gemm_set_l2_prefetch(int k_blocks) { g_l2_prefetch_kb = k_blocks < 0 ? 0 : k_blocks; }
+
 int atx_gemm_auto_splits(long long N, long long K, int T) {
-    // Decode-sized batches are pure weight streaming: cut K until roughly two CTAs per SM are
-    // resident so that every SM has TMA loads in flight, but keep >= 8 k-blocks (128 KB) per CTA.
+    // Decode-sized batches are pure weight streaming. Two CTAs fit per SM (shared memory), so cut K
+    // until the grid fills ONE wave of 2 x SMs CTAs (no tail wave), keeping >= 4 k-blocks per CTA.
     if (T > 64) return 1;
     const long long tiles = (N + kBM - 1) / kBM;
     const int kb = static_cast<int>(K / kBK);
-    const int target = 2 * num_sms();
-    int s = 1;
-    while (tiles * s < target && kb / (s * 2) >= 8) s *= 2;
-    return s;
+    const long long slots = 2ll * num_sms();
+    if (tiles >= slots) return 1;
+    int s = static_cast<int>(slots / tiles);
+    if (s > kb / 4) s = kb / 4;
+    if (s < 1) s = 1;
+    // make the split even: ceil(kb / s) blocks each, drop empty trailing splits
+    const int per = (kb + s - 1) / s;
+    return (kb + per - 1) / per;
 }
 
 int atx_gemm_run(const atx_gemm_plan* p, void* out, long long ldo, int T, int mode, int splits, int flags,
@@ -323,8 +375,9 @@ int atx_gemm_run(const atx_gemm_plan* p, void* out, long long ldo, int T, int mo
     cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
     ATX_REQUIRE(p && out, "atx_gemm_run: null pointer");
     ATX_REQUIRE(T > 0 && T <= p->T_cap, "atx_gemm_run: T=%d outside (0, %lld]", T, p->T_cap);
-    ATX_REQUIRE(mode >= ATX_GEMM_STORE_F32 && mode <= ATX_GEMM_STORE_BF16, "atx_gemm_run: bad mode %d", mode);
-    ATX_REQUIRE(ldo >= p->N, "atx_gemm_run: ldo=%lld < N=%lld", ldo, p->N);
+    ATX_REQUIRE(mode >= ATX_GEMM_STORE_F32 && mode <= ATX_GEMM_SWIGLU_BF16, "atx_gemm_run: bad mode %d", mode);
+    ATX_REQUIRE(ldo >= (mode == ATX_GEMM_SWIGLU_BF16 ? p->N / 2 : p->N), "atx_gemm_run: ldo=%lld too small for N=%lld", ldo, p->N);
+    ATX_REQUIRE(mode != ATX_GEMM_SWIGLU_BF16 || p->N % 128 == 0, "atx_gemm_run: SWIGLU mode needs N %% 128 == 0");
     if (splits <= 0) splits = (mode == ATX_GEMM_ADD_F32) ? atx_gemm_auto_splits(p->N, p->K, T) : 1;
     ATX_REQUIRE(splits == 1 || mode == ATX_GEMM_ADD_F32,
                 "atx_gemm_run: split-K (%d) needs ATX_GEMM_ADD_F32 into a zeroed or residual buffer", splits);

@@ -99,7 +99,7 @@ rope_kv_write_kernel(const float* __restrict__ qkv, const int* __restrict__ posi
     const float* cs = cos_sin + static_cast<long long>(pos) * D;
     const long long blk = slot >= 0 ? slot / block_size : 0;
     const int off = slot >= 0 ? slot % block_size : 0;
-    for (int w = threadIdx.x; w < n_rot + n_v; w += blockDim.x) {
+    for (int w = blockIdx.y * blockDim.x + threadIdx.x; w < n_rot + n_v; w += gridDim.y * blockDim.x) {
         if (w < n_rot) {
             const int h = w / per_head;
             const int i = (w % per_head) * 4;
@@ -210,7 +210,10 @@ int atx_rope_kv_write(const float* qkv, const int* positions, const int* slots, 
                 "atx_rope_kv_write: bad shape T=%d Hq=%d Hkv=%d D=%d block_size=%d", T, Hq, Hkv, D, block_size);
     cudaLaunchConfig_t cfg = {};
     cudaLaunchAttribute attr[1];
-    cfg.gridDim = dim3(static_cast<unsigned>(T));
+    // few tokens (decode): split each token's (Hq + 2 Hkv) * D / 4 work items over several CTAs
+    const int items = (Hq + Hkv) * (D / 8) + Hkv * (D / 4);
+    const int per_tok = T >= 512 ? 1 : (items + 255) / 256;
+    cfg.gridDim = dim3(static_cast<unsigned>(T), static_cast<unsigned>(per_tok));
     cfg.blockDim = dim3(256);
     cfg.stream = reinterpret_cast<cudaStream_t>(stream);
     set_pdl(cfg, attr, flags);

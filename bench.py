@@ -156,7 +156,7 @@ def gemm_roofline(engine, T: int, hbm_gbs: float) -> dict:
         for p_qkv, p_o, p_gu, p_down in r.plans:
             lib.atx_gemm_run(p_qkv._h, r.qkv.data_ptr(), m.qkv_size, T, 1, 0, r.flags, s)
             lib.atx_gemm_run(p_o._h, r.h.data_ptr(), H, T, 1, 0, r.flags, s)
-            lib.atx_gemm_run(p_gu._h, r.gu.data_ptr(), 2 * I, T, 1, 0, r.flags, s)
+            lib.atx_gemm_run(p_gu._h, r.act.data_ptr(), I, T, 3, 1, r.flags, s)
             lib.atx_gemm_run(p_down._h, r.h.data_ptr(), H, T, 1, 0, r.flags, s)
         lib.atx_gemm_run(r.plan_lm._h, r.logits.data_ptr(), V, T, 0, 1, r.flags, s)
 
@@ -174,7 +174,7 @@ def gemm_roofline(engine, T: int, hbm_gbs: float) -> dict:
     launches = 4 * m.num_hidden_layers + 1
     ms = e0.elapsed_time(e1) / iters
     act = T * 2 * (m.num_hidden_layers * (2 * H + m.q_size + I) + H)           # bf16 activations read
-    outb = T * 4 * (m.num_hidden_layers * (m.qkv_size + 2 * H + 2 * I) + V)    # fp32 results written
+    outb = T * (m.num_hidden_layers * (4 * m.qkv_size + 8 * H + 2 * I) + 4 * V)  # fp32 / bf16 results written
     byts = m.weight_bytes_per_decode_step() + act + outb
     achieved = byts / ms / 1e6
     traffic = None

@@ -48,6 +48,10 @@ typedef struct atx_gemm_plan atx_gemm_plan;
 #define ATX_GEMM_STORE_F32 0  /* out fp32 = acc                                            */
 #define ATX_GEMM_ADD_F32 1    /* out fp32 += acc (atomic; enables split-K; fuses residual) */
 #define ATX_GEMM_STORE_BF16 2 /* out bf16 = round(acc)                                     */
+/* Fused SwiGLU (modeling_llama.py:182-184): W holds gate and up rows INTERLEAVED in groups of 64
+ * (rows [128j, 128j+64) = gate[64j..], rows [128j+64, 128j+128) = up[64j..]); out is bf16
+ * [T, N/2] with out[t, 64j+i] = silu(acc_gate) * acc_up. No split-K. */
+#define ATX_GEMM_SWIGLU_BF16 3
 int atx_gemm_plan_create(atx_gemm_plan** plan, const void* W, long long N, long long K, const void* X,
                          long long T_cap, long long ldx);
 void atx_gemm_plan_destroy(atx_gemm_plan* plan);
@@ -55,6 +59,9 @@ void atx_gemm_plan_destroy(atx_gemm_plan* plan);
 int atx_gemm_run(const atx_gemm_plan* plan, void* out, long long ldo, int T, int mode, int splits,
                  int flags, atx_stream_t stream);
 int atx_gemm_auto_splits(long long N, long long K, int T);
+/* Tuning knob: how many 16 KB weight slices a CTA launched with ATX_FLAG_PDL prefetches into L2
+ * before it waits for the upstream kernel (default 16; 0 disables). Process-wide. */
+void atx_gemm_set_l2_prefetch(int k_blocks);
 
 /* ---- embedding gather: out[t, :] = float(table[ids[t], :]) ---------------------------------------
  * Replaces LlamaModel.embed_tokens (modeling_llama.py:375-427). table: [V, H] bf16, out fp32. */

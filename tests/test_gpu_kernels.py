@@ -72,6 +72,27 @@ def test_gemm_matches_fp32_reference(cabi, T, N, K, mode, splits):
     assert ref.shape == got.shape
 
 
+@pytest.mark.parametrize("T,I,K", [(6, 128, 256), (16, 1024, 512), (40, 192, 128), (300, 256, 1024)])
+def test_gemm_fused_swiglu_epilogue(cabi, T, I, K):
+    """ATX_GEMM_SWIGLU_BF16: interleaved gate/up rows, act = silu(x Wg^T) * (x Wu^T) in bf16."""
+    from atx.weights import interleave_gate_up
+
+    g = torch.Generator().manual_seed(T + I + K)
+    x = _bf16(torch.randn(T, K, generator=g))
+    wg = _bf16(torch.randn(I, K, generator=g) * 0.08)
+    wu = _bf16(torch.randn(I, K, generator=g) * 0.08)
+    xb = torch.zeros(max(T, 8), K, dtype=torch.bfloat16, device="cuda")
+    xb[:T] = x.cuda()
+    plan = cabi.GemmPlan(interleave_gate_up(wg, wu).cuda().contiguous(), xb)
+    out = torch.full((T, I), 7.0, dtype=torch.bfloat16, device="cuda")
+    plan.run(out, T, cabi.GEMM_SWIGLU_BF16, 1)
+    want = R.swiglu(x.float() @ wg.float().T, x.float() @ wu.float().T)
+    err = (out.float().cpu() - want).abs()
+    assert torch.all(err <= 2 ** -7 * want.abs() + 1e-3), float(err.max())
+    with pytest.raises(cabi.AtxError, match="split-K"):
+        plan.run(out, T, cabi.GEMM_SWIGLU_BF16, 2)
+
+
 def test_gemm_rows_beyond_T_do_not_leak(cabi):
     """Rows of the X buffer past T (stale data, even NaN) must not influence rows < T."""
     K, N, T = 256, 256, 5
