@@ -130,7 +130,7 @@ class ModelRunner:
         self.stream = torch.cuda.Stream(device=dev)   # every launch and copy of this runner
         self._h2d_done = torch.cuda.Event()
         self.flags = _cabi.FLAG_PDL if e.use_pdl else 0
-        self.lib.atx_gemm_set_l2_prefetch(int(os.environ.get("ATX_L2_PREFETCH_KB", "16")))
+        self.lib.atx_gemm_set_l2_prefetch(int(os.environ.get("ATX_L2_PREFETCH_KB", "0")))
         self.scale = float(m.head_dim) ** -0.5
         self.launches_last_step = 0
         self.kernel_launches = 0  # cumulative count of our kernels launched (graph replays included)

@@ -156,37 +156,47 @@ gemm_wt_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
         if (mode == ATX_GEMM_SWIGLU_BF16) {
             // Rows [0,64) of this tile are gate features, rows [64,128) the matching up features
             // (weights interleaved in 64-row groups at load time): act = silu(gate) * up, bf16.
-            // The up half crosses from warps 2-3 to warps 0-1 through the (now idle) stage buffers.
-            float* su = reinterpret_cast<float*>(smem);  // [TN][64]
-            if (warp >= 2) {
+            // The halves cross between warps 0-1 (gate lanes) and warps 2-3 (up lanes) through the
+            // (now idle) stage buffers. For TN >= 32 the exchange is symmetric so all four warps do
+            // the activation math: warps 0-1 finish token columns [0, TN/2), warps 2-3 the rest.
+            float* sx = reinterpret_cast<float*>(smem);  // [TN][64]: up for cols < HALF, gate for cols >= HALF
+            constexpr int HALF = TN >= 32 ? TN / 2 : TN;
+            const bool gate_warp = warp < 2;
+            const int i = (warp & 1) * 32 + lane;            // feature within the 64-group
+            const long long col = static_cast<long long>(blockIdx.x) * 64 + i;
+            const bool ok = col < N / 2;
+            __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out);
+            const uint32_t tlane = tmem_acc + (static_cast<uint32_t>(warp * 32) << 16);
+            // phase 1: park the half the OTHER pair of warps needs
+            {
+                const int c_lo = gate_warp ? HALF : 0, c_hi = gate_warp ? TN : HALF;
 #pragma unroll 1
-                for (int c = 0; c < TN; c += 16) {
+                for (int c = c_lo; c < c_hi; c += 16) {
                     if (t0 + c >= T) break;
                     uint32_t v[16];
-                    tmem_ld16(tmem_acc + (static_cast<uint32_t>(warp * 32) << 16) + c, v);
+                    tmem_ld16(tlane + c, v);
                     tmem_ld_wait();
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) su[(c + j) * 64 + (warp - 2) * 32 + lane] = __uint_as_float(v[j]);
+                    for (int j = 0; j < 16; ++j) sx[(c + j) * 64 + i] = __uint_as_float(v[j]);
                 }
             }
             __syncthreads();
-            if (warp < 2) {
-                const int i = warp * 32 + lane;                 // feature within the 64-group
-                const long long col = static_cast<long long>(blockIdx.x) * 64 + i;
-                const bool ok = col < N / 2;
-                __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out);
+            // phase 2: own half from TMEM, partner half from shared memory
+            {
+                const int c_lo = gate_warp ? 0 : HALF, c_hi = gate_warp ? HALF : TN;
 #pragma unroll 1
-                for (int c = 0; c < TN; c += 16) {
+                for (int c = c_lo; c < c_hi; c += 16) {
                     if (t0 + c >= T) break;
                     uint32_t v[16];
-                    tmem_ld16(tmem_acc + (static_cast<uint32_t>(warp * 32) << 16) + c, v);
+                    tmem_ld16(tlane + c, v);
                     tmem_ld_wait();
 #pragma unroll
                     for (int j = 0; j < 16; ++j) {
                         const int t = t0 + c + j;
-                        const float g = __uint_as_float(v[j]);
-                        const float a = g / (1.f + expf(-g)) * su[(c + j) * 64 + i];
-                        if (ok && t < T) o[static_cast<long long>(t) * ldo + col] = __float2bfloat16_rn(a);
+                        const float mine = __uint_as_float(v[j]), other = sx[(c + j) * 64 + i];
+                        const float g = gate_warp ? mine : other, u = gate_warp ? other : mine;
+                        if (ok && t < T)
+                            o[static_cast<long long>(t) * ldo + col] = __float2bfloat16_rn(g / (1.f + expf(-g)) * u);
                     }
                 }
             }
@@ -289,7 +299,7 @@ struct atx_gemm_plan {
 using namespace atx;
 
 // k-blocks (16 KB each) of weights a CTA prefetches into L2 before it waits for the upstream grid
-static int g_l2_prefetch_kb = 16;
+static int g_l2_prefetch_kb = 0;  // measured on B200: prefetching ahead of the TMA ring costs bandwidth (r01)
 
 template <int TN>
 static int launch_gemm(const atx_gemm_plan* p, int ti, void* out, long long ldo, int T, int mode,

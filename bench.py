@@ -102,6 +102,25 @@ class ClockSampler(threading.Thread):
                 "reasons": rs, "samples": len(self.samples)}
 
 
+def max_over_ranks(dist, values, device):
+    """Element-wise MAX of a list of floats over all ranks (identity without a process group)."""
+    import torch
+
+    t = torch.tensor(list(values), dtype=torch.float64, device=device)
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return [float(x) for x in t]
+
+
+def gather_over_ranks(dist, items, world):
+    """Concatenate a python list from every rank (rank order)."""
+    if dist is None:
+        return list(items)
+    parts = [None] * world
+    dist.all_gather_object(parts, list(items))
+    return [x for part in parts for x in part]
+
+
 # ------------------------------------------------------------------------------------------------------
 def run_burst(engine, prompts):
     """Submit the burst and step the engine to completion. Returns the finished sequences."""
@@ -321,13 +340,8 @@ def main() -> None:
     launches = r.kernel_launches - l0
     eng_steps = engine.steps - s0
     step_events, r.step_events = r.step_events, None
-    t = torch.tensor([dev_ms, host_ms], device="cuda")
-    if dist is not None:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        all_ttft = [None] * world
-        dist.all_gather_object(all_ttft, ttfts)
-        ttfts = [x for part in all_ttft for x in part]
-    dev_ms = float(t[0])
+    dev_ms, host_ms = max_over_ranks(dist, [dev_ms, host_ms], "cuda")
+    ttfts = gather_over_ranks(dist, ttfts, world)
     tokens = args.steps * BATCH * OUT * world
     value = tokens / (dev_ms / 1e3)
 
@@ -371,15 +385,14 @@ def main() -> None:
             barrier()
             wall = time.perf_counter() - tw
         aeng.shutdown()
-        tw_t = torch.tensor([wall], device="cuda")
-        if dist is not None:
-            dist.all_reduce(tw_t, op=dist.ReduceOp.MAX)
+        wall = max_over_ranks(dist, [wall], "cuda")[0]
         flat = [m for burst in metas for m in burst]
+        e2e_ttft = gather_over_ranks(dist, [m["queue_wait_s"] for m in flat], world)
         assert all(m["completion_tokens"] == OUT and m["prompt_tokens"] == PROMPT for m in flat)
-        e2e = {"value": round(tokens / float(tw_t[0]), 1), "unit": UNIT,
+        e2e = {"value": round(tokens / wall, 1), "unit": UNIT,
                "h2d_bytes_per_step": round((r.h2d_bytes - h0) / args.steps),
                "d2h_bytes_per_step": round((r.d2h_bytes - d0) / args.steps),
-               "ttft_p50_ms": round(1e3 * statistics.median(m["queue_wait_s"] for m in flat), 2),
+               "ttft_p50_ms": round(1e3 * statistics.median(e2e_ttft), 2),
                "path": "HTTP POST /chat on 127.0.0.1 (aiohttp server + client), text prompts, byte tokenizer"}
 
     cpu = None
@@ -405,7 +418,7 @@ def main() -> None:
                        "kv_blocks": r.num_blocks},
             "ttft_p50_ms": round(1e3 * statistics.median(ttfts), 2),
             "ttft_max_ms": round(1e3 * max(ttfts), 2),
-            "host_ms_per_step": round(float(t[1]) / args.steps, 3),
+            "host_ms_per_step": round(host_ms / args.steps, 3),
             "gpu_launches": launches, "engine_steps": eng_steps,
             "clocks": clocks, "roofline": roof, "decode_step": decode_step, "prefill": prefill, "e2e": e2e,
             "cpu_baseline": cpu,

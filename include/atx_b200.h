@@ -60,7 +60,7 @@ int atx_gemm_run(const atx_gemm_plan* plan, void* out, long long ldo, int T, int
                  int flags, atx_stream_t stream);
 int atx_gemm_auto_splits(long long N, long long K, int T);
 /* Tuning knob: how many 16 KB weight slices a CTA launched with ATX_FLAG_PDL prefetches into L2
- * before it waits for the upstream kernel (default 16; 0 disables). Process-wide. */
+ * before it waits for the upstream kernel (default 0 = off: it measured slower on B200). Process-wide. */
 void atx_gemm_set_l2_prefetch(int k_blocks);
 
 /* ---- embedding gather: out[t, :] = float(table[ids[t], :]) ---------------------------------------

@@ -37,3 +37,26 @@ class FakeAsyncEngine:
             out.append(ord("a") + (len(prompt_ids) + i) % 26)
             yield RequestOutput(request_id, list(out), out[-1:], i == n - 1, "length" if i == n - 1 else None,
                                 len(prompt_ids), 0, None)
+
+
+def fake_replica_worker(rank, model, ecfg, req, resp):
+    """Stands in for atx.router._engine_worker in CPU tests: echoes `max_tokens` ids tagged with the
+    replica rank so tests can see where a request was routed. `model == "explode"` dies on the first
+    request to exercise failure propagation."""
+    resp.send(("ready", rank, (100 + rank, 16), 1024))
+    while True:
+        msg = req.recv()
+        if msg[0] == "stop":
+            return
+        if msg[0] == "add":
+            _, rid, ids, params = msg
+            if model == "explode":
+                resp.send(("fatal", rank, "boom"))
+                return
+            if len(ids) > 500:
+                resp.send(("error", rid, "ValueError('too long')"))
+                continue
+            n = params.max_tokens
+            for i in range(n):
+                toks = [1000 * rank + i] if i < n - 1 else [1000 * rank + j for j in range(n)]
+                resp.send(("out", rid, toks, i == n - 1, "length" if i == n - 1 else None, len(ids), 0))
