@@ -27,6 +27,7 @@ EXPORTS = [
     "atx_gemm_set_l2_prefetch",
     "atx_embed_gather", "atx_rmsnorm", "atx_rope_kv_write", "atx_silu_mul",
     "atx_paged_attn_decode_workspace_bytes", "atx_paged_attn_decode", "atx_paged_attn_prefill",
+    "atx_paged_attn_decode_static", "atx_paged_attn_decode_static_capacity",
     "atx_sample",
 ]
 
@@ -78,6 +79,9 @@ def load() -> C.CDLL:
     lib.atx_paged_attn_decode_workspace_bytes.restype = i64
     lib.atx_paged_attn_decode.argtypes = [vp, vp, vp, vp, vp, vp, vp, i64, i32, i32, i32, i32, i32, i32, i32, f32,
                                           i32, vp]
+    lib.atx_paged_attn_decode_static.argtypes = [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, f32, i32, vp]
+    lib.atx_paged_attn_decode_static_capacity.argtypes = []
+    lib.atx_paged_attn_decode_static_capacity.restype = i64
     lib.atx_paged_attn_prefill.argtypes = [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, f32, i32,
                                            vp]
     lib.atx_sample.argtypes = [vp, i64, vp, vp, vp, vp, vp, i32, i32, i32, vp]
@@ -189,6 +193,24 @@ def paged_attn_decode(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Ten
     _check(load().atx_paged_attn_decode(q.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(), block_table.data_ptr(),
                                         seq_lens.data_ptr(), out.data_ptr(), _p(workspace), wsb, B, Hq, Hkv, D,
                                         block_size, block_table.shape[1], num_splits, scale, flags, _stream()))
+
+
+def paged_attn_decode_static(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, block_table: torch.Tensor,
+                             seq_lens: torch.Tensor, out: torch.Tensor, B: int, Hq: int, Hkv: int, D: int,
+                             block_size: int, num_splits: int, scale: float, flags: int = 0) -> None:
+    """Decode attention whose split scratch is the library's built-in 8 MiB array: for callers that
+    cannot allocate device memory (see include/atx_b200.h). Calls on one device must not overlap."""
+    _dev(q, k_cache, v_cache, block_table, seq_lens, out)
+    assert q.dtype == torch.bfloat16 and out.dtype == torch.bfloat16 and block_table.dtype == torch.int32
+    assert seq_lens.dtype == torch.int32
+    _check(load().atx_paged_attn_decode_static(q.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(),
+                                               block_table.data_ptr(), seq_lens.data_ptr(), out.data_ptr(), B, Hq,
+                                               Hkv, D, block_size, block_table.shape[1], num_splits, scale, flags,
+                                               _stream()))
+
+
+def decode_static_capacity() -> int:
+    return int(load().atx_paged_attn_decode_static_capacity())
 
 
 def paged_attn_prefill(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, block_table: torch.Tensor,

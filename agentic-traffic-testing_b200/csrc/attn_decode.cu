@@ -12,6 +12,8 @@
 // attn_decode_reduce_kernel.
 #include "common.cuh"
 
+#include <mutex>
+
 #include "../../include/atx_b200.h"
 
 namespace atx {
@@ -313,6 +315,96 @@ int atx_paged_attn_decode(const void* q, const void* kc, const void* vc, const i
     ATX_DEC_CASE(64, 8)
 #undef ATX_DEC_CASE
     set_error("atx_paged_attn_decode: unsupported head_dim=%d / group=%d (head_dim 64|128, group 1|2|4|8)", D, G);
+    return ATX_ERR_UNSUPPORTED;
+}
+
+// ---- decode attention without any allocation -----------------------------------------------------
+// Some hosts of this library can hand us pointers but cannot obtain device memory themselves: a
+// server that has already given every free byte of HBM to its KV pool, a process running under a
+// fixed memory reservation where a late cudaMalloc fails, a request path that must not take
+// cudaMalloc's device-wide synchronisation, or a foreign-language binding (cgo / JNI / N-API) that
+// has no CUDA runtime of its own to allocate the split-KV scratch with. For them the partial
+// results of the KV splits live in the array below, which is part of the library image: every GPU
+// that loads libatx_b200.so holds these 8 MiB until the process exits.
+constexpr long long kStaticScratchBytes = 8ll << 20;
+static __device__ __align__(256) float g_decode_scratch[kStaticScratchBytes / 4];
+
+// `g_decode_scratch` in host code is only a handle for the runtime, not an address a kernel may
+// dereference, so the device address is looked up once per device (with that device current).
+static float* static_scratch_for_current_device(int* rc) {
+    static std::mutex mu;
+    static float* ptr[64] = {nullptr};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) {
+        *rc = cuda_fail(e, "cudaGetDevice");
+        return nullptr;
+    }
+    if (dev < 0 || dev >= 64) {
+        set_error("atx_paged_attn_decode_static: device ordinal %d is outside the supported range [0, 64)", dev);
+        *rc = ATX_ERR_LIMIT;
+        return nullptr;
+    }
+    std::lock_guard<std::mutex> lock(mu);
+    if (ptr[dev] == nullptr) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_decode_scratch);
+        if (e != cudaSuccess) {
+            *rc = cuda_fail(e, "cudaGetSymbolAddress(g_decode_scratch)");
+            return nullptr;
+        }
+        ptr[dev] = static_cast<float*>(p);
+    }
+    *rc = ATX_OK;
+    return ptr[dev];
+}
+
+long long atx_paged_attn_decode_static_capacity(void) { return kStaticScratchBytes; }
+
+int atx_paged_attn_decode_static(const void* q, const void* kc, const void* vc, const int* bt, const int* sl,
+                                 void* out, int B, int Hq, int Hkv, int D, int block_size, int max_blocks,
+                                 int num_splits, float scale, int flags, atx_stream_t stream_) {
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    ATX_REQUIRE(q && kc && vc && bt && sl && out, "atx_paged_attn_decode_static: null pointer");
+    ATX_REQUIRE(B > 0 && Hq > 0 && Hkv > 0 && Hq % Hkv == 0 && block_size > 0 && max_blocks > 0 && num_splits > 0,
+                "atx_paged_attn_decode_static: bad shape B=%d Hq=%d Hkv=%d block_size=%d max_blocks=%d splits=%d", B,
+                Hq, Hkv, block_size, max_blocks, num_splits);
+    ATX_REQUIRE(num_splits <= 65535 && B <= 65535, "atx_paged_attn_decode_static: B and num_splits must be <= 65535");
+    const long long need = atx_paged_attn_decode_workspace_bytes(B, Hq, D, num_splits);
+    if (need > kStaticScratchBytes) {
+        set_error("atx_paged_attn_decode_static: B=%d Hq=%d D=%d num_splits=%d needs %lld bytes of split scratch, the "
+                  "built-in array holds %lld; use fewer splits / a smaller batch, or atx_paged_attn_decode with "
+                  "caller-provided scratch",
+                  B, Hq, D, num_splits, need, kStaticScratchBytes);
+        return ATX_ERR_LIMIT;
+    }
+    float* ws_o = nullptr;
+    float* ws_ml = nullptr;
+    if (num_splits > 1) {
+        int rc = ATX_OK;
+        float* base = static_scratch_for_current_device(&rc);
+        if (base == nullptr) return rc;
+        // Nothing in the scratch has to start at zero: every (head, split) slot that the merge
+        // kernel reads is rewritten by this call's own attention kernel first.
+        ws_o = base;
+        ws_ml = ws_o + static_cast<long long>(B) * Hq * num_splits * D;
+    }
+    const int G = Hq / Hkv;
+#define ATX_DEC_STATIC_CASE(DD, GG)                                                                           \
+    if (D == DD && G == GG)                                                                                    \
+        return launch_decode<DD, GG>(q, kc, vc, bt, sl, out, ws_o, ws_ml, B, Hq, Hkv, block_size, max_blocks, \
+                                     num_splits, scale, flags, stream);
+    ATX_DEC_STATIC_CASE(128, 4)
+    ATX_DEC_STATIC_CASE(128, 8)
+    ATX_DEC_STATIC_CASE(64, 4)
+    ATX_DEC_STATIC_CASE(128, 1)
+    ATX_DEC_STATIC_CASE(128, 2)
+    ATX_DEC_STATIC_CASE(64, 1)
+    ATX_DEC_STATIC_CASE(64, 2)
+    ATX_DEC_STATIC_CASE(64, 8)
+#undef ATX_DEC_STATIC_CASE
+    set_error("atx_paged_attn_decode_static: unsupported head_dim=%d / group=%d (head_dim 64|128, group 1|2|4|8)", D,
+              G);
     return ATX_ERR_UNSUPPORTED;
 }
 

@@ -101,6 +101,28 @@ int atx_paged_attn_decode(const void* q, const void* k_cache, const void* v_cach
                           int B, int Hq, int Hkv, int D, int block_size, int max_blocks, int num_splits,
                           float scale, int flags, atx_stream_t stream);
 
+/* Decode attention for callers that cannot allocate device memory. (No counterpart in the reference:
+ * it exists for hosts of this library, not for parity.) Same arithmetic and arguments as
+ * atx_paged_attn_decode, but the per-split partial results are kept in an 8 MiB array that is built
+ * into the library (resident on every GPU that loads it, until the process exits) instead of in a
+ * caller buffer — for processes that have already committed all of their HBM (e.g. to a KV pool),
+ * run under a fixed memory reservation, must avoid cudaMalloc's device-wide synchronisation on the
+ * request path, or bind this ABI from a language runtime with no CUDA allocator of its own.
+ *   - Limit: atx_paged_attn_decode_workspace_bytes(B, Hq, D, num_splits) must not exceed
+ *     atx_paged_attn_decode_static_capacity() (8 MiB); larger requests return ATX_ERR_LIMIT with the
+ *     sizes spelled out in atx_last_error(). It never calls cudaMalloc / cudaFree.
+ *   - The first call on each device looks up the array's device address (one host-side runtime
+ *     query, with that device current); make that first call before starting any stream capture.
+ *   - All calls on a device share the one array and it keeps whatever the last call left in it.
+ *     Nothing needs clearing between calls (each call overwrites every slot it later reads), but two
+ *     calls whose kernels overlap on the GPU — different streams, or different host threads — race
+ *     on it: serialise them (same stream, or an event) or use the caller-scratch entry point. */
+long long atx_paged_attn_decode_static_capacity(void);
+int atx_paged_attn_decode_static(const void* q, const void* k_cache, const void* v_cache,
+                                 const int* block_table, const int* seq_lens, void* out, int B, int Hq,
+                                 int Hkv, int D, int block_size, int max_blocks, int num_splits, float scale,
+                                 int flags, atx_stream_t stream);
+
 /* ---- paged attention, prefill / chunked prefill (causal) ------------------------------------------
  * Same arithmetic as above with the causal mask of create_causal_mask; queries of sequence s are
  * rows [cu_q[s], cu_q[s+1]) of q, and their keys are the first ctx_lens[s] cache tokens of that
