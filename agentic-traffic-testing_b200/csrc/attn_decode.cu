@@ -223,6 +223,185 @@ attn_decode_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __r
     }
 }
 
+// ---- tensor-core decode attention --------------------------------------------------------------------
+// The CUDA-core kernel above issues ~90 warp instructions per (token, kv-head) row of 512 bytes; at
+// 6.5 TB/s that is the whole issue bandwidth of the chip (ncu: issue slots 65 % busy, DRAM 7 %), so it
+// can never be HBM-bound. Here the G query heads of one KV head become rows of a 16-row MMA tile
+// (rows >= G are zero padding): QK^T and PV run on mma.sync m16n8k16 and one warp needs ~8 instructions
+// per row. One WARP per CTA (no block-level merge), K/V pages staged with cp.async into a 3-deep ring
+// of XOR-swizzled 16-token tiles, read back with ldmatrix. Requires block_size % 16 == 0 so that a
+// tile never straddles a page; other block sizes keep using attn_decode_kernel.
+__device__ __forceinline__ void dec_cp_async16(void* smem_dst, const void* gsrc, bool valid) {
+    const uint32_t sz = valid ? 16u : 0u;  // src-size 0 => zero fill: stale page rows (even NaN) never reach P.V
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(sz)
+                 : "memory");
+}
+__device__ __forceinline__ void dec_ldsm_x4(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3)
+                 : "r"(addr));
+}
+__device__ __forceinline__ void dec_ldsm_x4_t(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3)
+                 : "r"(addr));
+}
+__device__ __forceinline__ void dec_mma(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0,
+                                        uint32_t b1) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, "
+        "{%0, %1, %2, %3};"
+        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+        : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+constexpr int kMmaTile = 16;    // tokens per tile
+constexpr int kMmaStages = 3;
+
+template <int D>
+__global__ void __launch_bounds__(32)
+attn_decode_mma_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __restrict__ k_cache,
+                       const __nv_bfloat16* __restrict__ v_cache, const int* __restrict__ block_table,
+                       const int* __restrict__ seq_lens, __nv_bfloat16* __restrict__ out, float* __restrict__ ws_o,
+                       float* __restrict__ ws_ml, int Hq, int Hkv, int block_size, int max_blocks, int num_splits,
+                       float scale_log2) {
+    constexpr int CH = D / 8;                     // 16-byte chunks per row
+    constexpr int TILE_BYTES = kMmaTile * D * 2;  // one K (or V) tile
+    __shared__ __align__(128) uint8_t smem[kMmaStages * 2 * TILE_BYTES];
+
+    pdl_launch_dependents();
+    pdl_wait();
+    const int g = blockIdx.x, b = blockIdx.y, sp = blockIdx.z;
+    const int lane = threadIdx.x;
+    const int gid = lane >> 2, tig = lane & 3;
+    const int G = Hq / Hkv;
+    const int L = seq_lens[b];
+    int chunk = (L + num_splits - 1) / num_splits;
+    chunk = (chunk + kMmaTile - 1) / kMmaTile * kMmaTile;
+    const int begin = sp * chunk;
+    const int end = min(L, begin + chunk);
+    const int n_tiles = end > begin ? (end - begin + kMmaTile - 1) / kMmaTile : 0;
+    const int* bt = block_table + static_cast<long long>(b) * max_blocks;
+
+    auto issue_tile = [&](int t) {
+        // a 16-token tile lies inside one page: one block-table lookup, rows are contiguous
+        const int tok0 = begin + t * kMmaTile;
+        const int page = __ldg(bt + tok0 / block_size);
+        const long long base = ((static_cast<long long>(page) * Hkv + g) * block_size + tok0 % block_size) * D;
+        uint8_t* sk = smem + (t % kMmaStages) * 2 * TILE_BYTES;
+        uint8_t* sv = sk + TILE_BYTES;
+#pragma unroll
+        for (int i = lane; i < kMmaTile * CH; i += 32) {
+            const int r = i / CH, c = i % CH;
+            const uint32_t so = static_cast<uint32_t>(r * (D * 2) + ((c ^ (r & 7)) << 4));
+            const bool valid = tok0 + r < end;
+            dec_cp_async16(sk + so, k_cache + base + r * D + c * 8, valid);
+            dec_cp_async16(sv + so, v_cache + base + r * D + c * 8, valid);
+        }
+    };
+#pragma unroll
+    for (int t = 0; t < kMmaStages - 1; ++t) {
+        if (t < n_tiles) issue_tile(t);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+
+    // Q as the A operand: row gid = query head gid of this KV head (zero rows beyond G)
+    uint32_t qa[D / 16][2];
+    {
+        const uint32_t* qrow =
+            reinterpret_cast<const uint32_t*>(q + (static_cast<long long>(b) * Hq + g * G + min(gid, G - 1)) * D);
+#pragma unroll
+        for (int kk = 0; kk < D / 16; ++kk) {
+            qa[kk][0] = gid < G ? __ldg(qrow + kk * 8 + tig) : 0u;
+            qa[kk][1] = gid < G ? __ldg(qrow + kk * 8 + 4 + tig) : 0u;
+        }
+    }
+    float o_acc[D / 8][4];
+#pragma unroll
+    for (int i = 0; i < D / 8; ++i) o_acc[i][0] = o_acc[i][1] = o_acc[i][2] = o_acc[i][3] = 0.f;
+    float m_run = -INFINITY, l_run = 0.f;
+
+    for (int t = 0; t < n_tiles; ++t) {
+        if (t + kMmaStages - 1 < n_tiles) issue_tile(t + kMmaStages - 1);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        asm volatile("cp.async.wait_group %0;" ::"n"(kMmaStages - 1) : "memory");
+        __syncwarp();
+        const uint8_t* sk = smem + (t % kMmaStages) * 2 * TILE_BYTES;
+        const uint8_t* sv = sk + TILE_BYTES;
+
+        float sc[2][4];
+#pragma unroll
+        for (int nb = 0; nb < 2; ++nb) sc[nb][0] = sc[nb][1] = sc[nb][2] = sc[nb][3] = 0.f;
+#pragma unroll
+        for (int kk = 0; kk < D / 16; ++kk) {
+            uint32_t b0, b1, b2, b3;
+            const int r = (lane & 7) + (lane >> 4) * 8;
+            const int c = kk * 2 + ((lane >> 3) & 1);
+            dec_ldsm_x4(smem_u32(sk + r * (D * 2) + ((c ^ (r & 7)) << 4)), b0, b1, b2, b3);
+            dec_mma(sc[0], qa[kk][0], 0u, qa[kk][1], 0u, b0, b1);
+            dec_mma(sc[1], qa[kk][0], 0u, qa[kk][1], 0u, b2, b3);
+        }
+        // rows gid (valid heads); mask tokens past the end of this split
+        const int tok0 = begin + t * kMmaTile;
+        float mx = -INFINITY;
+#pragma unroll
+        for (int nb = 0; nb < 2; ++nb) {
+            const int col = tok0 + nb * 8 + 2 * tig;
+            if (col >= end) sc[nb][0] = -INFINITY;
+            if (col + 1 >= end) sc[nb][1] = -INFINITY;
+            mx = fmaxf(mx, fmaxf(sc[nb][0], sc[nb][1]));
+        }
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+        const float mn = fmaxf(m_run, mx);  // finite: the first token of a tile is always < end
+        const float mref = mn * scale_log2;
+        const float corr = exp2f(m_run * scale_log2 - mref);
+        m_run = mn;
+        const float p00 = exp2f(sc[0][0] * scale_log2 - mref), p01 = exp2f(sc[0][1] * scale_log2 - mref);
+        const float p10 = exp2f(sc[1][0] * scale_log2 - mref), p11 = exp2f(sc[1][1] * scale_log2 - mref);
+        l_run = l_run * corr + (p00 + p01) + (p10 + p11);
+        const uint32_t pa0 = pack_bf16(p00, p01), pa2 = pack_bf16(p10, p11);
+#pragma unroll
+        for (int db = 0; db < D / 8; ++db) {
+            o_acc[db][0] *= corr;
+            o_acc[db][1] *= corr;
+        }
+#pragma unroll
+        for (int db2 = 0; db2 < D / 16; ++db2) {
+            uint32_t b0, b1, b2, b3;
+            const int r = (lane & 7) + ((lane >> 3) & 1) * 8;
+            const int c = db2 * 2 + (lane >> 4);
+            dec_ldsm_x4_t(smem_u32(sv + r * (D * 2) + ((c ^ (r & 7)) << 4)), b0, b1, b2, b3);
+            dec_mma(o_acc[2 * db2], pa0, 0u, pa2, 0u, b0, b1);
+            dec_mma(o_acc[2 * db2 + 1], pa0, 0u, pa2, 0u, b2, b3);
+        }
+        __syncwarp();  // all lanes done reading this stage before it is refilled
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+
+    l_run += __shfl_xor_sync(0xffffffffu, l_run, 1);
+    l_run += __shfl_xor_sync(0xffffffffu, l_run, 2);
+    if (gid < G) {
+        const long long h = static_cast<long long>(b) * Hq + g * G + gid;
+        if (num_splits == 1) {
+            const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
+#pragma unroll
+            for (int db = 0; db < D / 8; ++db)
+                *reinterpret_cast<uint32_t*>(out + h * D + db * 8 + 2 * tig) =
+                    pack_bf16(o_acc[db][0] * inv, o_acc[db][1] * inv);
+        } else {
+            float* po = ws_o + (h * num_splits + sp) * D;
+#pragma unroll
+            for (int db = 0; db < D / 8; ++db)
+                *reinterpret_cast<float2*>(po + db * 8 + 2 * tig) = make_float2(o_acc[db][0], o_acc[db][1]);
+            if (tig == 0) {
+                ws_ml[(h * num_splits + sp) * 2] = m_run == -INFINITY ? -INFINITY : m_run * scale_log2;
+                ws_ml[(h * num_splits + sp) * 2 + 1] = l_run;
+            }
+        }
+    }
+}
+
 // out[h, :] = sum_s o_s * 2^(m_s - M) / sum_s l_s * 2^(m_s - M)
 __global__ void attn_decode_reduce_kernel(const float* __restrict__ ws_o, const float* __restrict__ ws_ml,
                                           __nv_bfloat16* __restrict__ out, int D, int num_splits) {
@@ -254,12 +433,21 @@ static int launch_decode(const void* q, const void* kc, const void* vc, const in
     cfg.attrs = attr;
     cfg.numAttrs = (flags & ATX_FLAG_PDL) ? 1 : 0;
     cfg.gridDim = dim3(static_cast<unsigned>(Hkv), static_cast<unsigned>(B), static_cast<unsigned>(num_splits));
-    cfg.blockDim = dim3(kDecThreads);
     cfg.stream = stream;
+    if (block_size % kMmaTile == 0 && G <= 8) {
+        cfg.blockDim = dim3(32);
+        ATX_CUDA(cudaLaunchKernelEx(&cfg, attn_decode_mma_kernel<D>, reinterpret_cast<const __nv_bfloat16*>(q),
+                                    reinterpret_cast<const __nv_bfloat16*>(kc),
+                                    reinterpret_cast<const __nv_bfloat16*>(vc), bt, sl,
+                                    reinterpret_cast<__nv_bfloat16*>(out), ws_o, ws_ml, Hq, Hkv, block_size, max_blocks,
+                                    num_splits, scale * 1.4426950408889634f));
+    } else {
+    cfg.blockDim = dim3(kDecThreads);
     ATX_CUDA(cudaLaunchKernelEx(&cfg, attn_decode_kernel<D, G>, reinterpret_cast<const __nv_bfloat16*>(q),
                                 reinterpret_cast<const __nv_bfloat16*>(kc), reinterpret_cast<const __nv_bfloat16*>(vc),
                                 bt, sl, reinterpret_cast<__nv_bfloat16*>(out), ws_o, ws_ml, Hq, Hkv, block_size,
                                 max_blocks, num_splits, scale * 1.4426950408889634f));
+    }
     if (num_splits > 1) {
         cfg.gridDim = dim3(static_cast<unsigned>(B * Hq));
         cfg.blockDim = dim3(static_cast<unsigned>(D));
