@@ -72,7 +72,7 @@ def load() -> C.CDLL:
     lib.atx_gemm_set_l2_prefetch.argtypes = [i32]
     lib.atx_gemm_set_l2_prefetch.restype = None
     lib.atx_embed_gather.argtypes = [vp, vp, vp, i32, i32, i32, vp]
-    lib.atx_rmsnorm.argtypes = [vp, vp, vp, vp, i32, i32, f32, vp, i64, i32, vp]
+    lib.atx_rmsnorm.argtypes = [vp, vp, vp, vp, vp, i32, i32, f32, vp, i64, i32, vp]
     lib.atx_rope_kv_write.argtypes = [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp]
     lib.atx_silu_mul.argtypes = [vp, vp, i32, i32, i32, vp]
     lib.atx_paged_attn_decode_workspace_bytes.argtypes = [i32, i32, i32, i32]
@@ -153,12 +153,13 @@ def embed_gather(ids: torch.Tensor, table: torch.Tensor, out: torch.Tensor, T: i
 
 def rmsnorm(x: torch.Tensor, w: torch.Tensor, out: torch.Tensor, T: int, eps: float,
             rows: Optional[torch.Tensor] = None, zero: Optional[torch.Tensor] = None, zero_bytes: int = 0,
-            flags: int = 0) -> None:
-    _dev(x, w, out, rows, zero)
+            flags: int = 0, add: Optional[torch.Tensor] = None) -> None:
+    _dev(x, w, out, rows, zero, add)
+    assert add is None or (add.dtype == torch.float32 and add.shape[-1] == x.shape[-1])
     assert x.dtype == torch.float32 and w.dtype == torch.bfloat16 and out.dtype == torch.bfloat16
     if zero is not None and zero_bytes == 0:
         zero_bytes = zero.numel() * zero.element_size()
-    _check(load().atx_rmsnorm(x.data_ptr(), _p(rows), w.data_ptr(), out.data_ptr(), T, x.shape[-1], eps, _p(zero),
+    _check(load().atx_rmsnorm(x.data_ptr(), _p(add), _p(rows), w.data_ptr(), out.data_ptr(), T, x.shape[-1], eps, _p(zero),
                               zero_bytes, flags, _stream()))
 
 

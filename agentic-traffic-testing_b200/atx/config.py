@@ -173,3 +173,5 @@ class EngineConfig:
     enable_cuda_graphs: bool = True
     use_pdl: bool = True
     device: int = 0
+    tp_size: int = 1          # tensor-parallel ranks sharing one model (70B); needs torch.distributed NCCL
+    tp_rank: int = 0

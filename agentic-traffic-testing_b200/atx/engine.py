@@ -42,9 +42,10 @@ class LLMEngine:
         torch.cuda.set_device(dev)
         if weights is None:
             if source.path is not None:
-                weights = ModelWeights.from_hf_dir(self.mcfg, source.path, dev)
+                weights = ModelWeights.from_hf_dir(self.mcfg, source.path, dev, ecfg.tp_size, ecfg.tp_rank)
             else:
-                weights = ModelWeights.random(self.mcfg, source.random_seed or 0, dev)
+                weights = ModelWeights.random(self.mcfg, source.random_seed or 0, dev, tp_size=ecfg.tp_size,
+                                              tp_rank=ecfg.tp_rank)
         self.runner = ModelRunner(self.mcfg, ecfg, weights)
         self.allocator = BlockAllocator(self.runner.num_blocks, ecfg.block_size, ecfg.enable_prefix_caching)
         self.scheduler = Scheduler(self.allocator, ecfg.max_num_seqs, ecfg.max_num_batched_tokens, ecfg.max_model_len,

@@ -55,23 +55,38 @@ class ModelRunner:
         self.Smax = max(1, e.max_num_seqs)
         self.bs = e.block_size
         self.MB = (e.max_model_len + self.bs - 1) // self.bs
-        H, I, V = m.hidden_size, m.intermediate_size, m.vocab_size
+        self.tp, self.tp_rank, self.tp_group = max(1, e.tp_size), e.tp_rank, None
+        tp = self.tp
+        if tp > 1:
+            import torch.distributed as dist
+
+            if not dist.is_initialized() or dist.get_world_size() % tp:
+                raise RuntimeError("tensor parallelism needs an initialised NCCL process group (torchrun)")
+            if m.num_key_value_heads % tp or m.intermediate_size % (64 * tp) or m.vocab_size % tp:
+                raise ValueError(f"tp_size={tp} must divide kv heads, intermediate_size/64 and the vocabulary")
+            first = dist.get_rank() // tp * tp
+            self.tp_group = dist.new_group(list(range(first, first + tp))) if dist.get_world_size() != tp else None
+        H, I, V = m.hidden_size, m.intermediate_size // tp, m.vocab_size
+        q_size = m.q_size // tp
+        qkv_size = m.qkv_size // tp
         bf, f32, i32 = torch.bfloat16, torch.float32, torch.int32
         dev = self.dev
         T, S = self.Tmax, max(self.Smax, 16)
         self.h = torch.zeros(T, H, dtype=f32, device=dev)
         self.xn = torch.zeros(T, H, dtype=bf, device=dev)
-        self.qkv = torch.zeros(T, m.qkv_size, dtype=f32, device=dev)
-        self.q = torch.zeros(T, m.q_size, dtype=bf, device=dev)
-        self.attn = torch.zeros(T, m.q_size, dtype=bf, device=dev)
+        self.qkv = torch.zeros(T, qkv_size, dtype=f32, device=dev)
+        self.q = torch.zeros(T, q_size, dtype=bf, device=dev)
+        self.attn = torch.zeros(T, q_size, dtype=bf, device=dev)
         self.act = torch.zeros(T, I, dtype=bf, device=dev)
+        self.part = torch.zeros(T, H, dtype=f32, device=dev) if tp > 1 else None  # partial o/down sums (TP)
+        self.allreduce_calls = 0
         self.xl = torch.zeros(S, H, dtype=bf, device=dev)
         self.logits = torch.zeros(S, V, dtype=f32, device=dev)
         self.out_ids = torch.zeros(S, dtype=i32, device=dev)
         self.out_host = torch.zeros(S, dtype=i32).pin_memory()
         self.rope = rope_table(m, e.max_model_len, dev)
         self.max_splits = 32
-        self.ws = torch.zeros(max(1, _cabi.decode_workspace_bytes(S, m.num_attention_heads, m.head_dim,
+        self.ws = torch.zeros(max(1, _cabi.decode_workspace_bytes(S, m.num_attention_heads // tp, m.head_dim,
                                                                   self.max_splits) // 4), dtype=f32, device=dev)
 
         # ---- staged integer / float inputs: one pinned host mirror, one device buffer -----------
@@ -110,7 +125,7 @@ class ModelRunner:
         self.plan_lm = _cabi.GemmPlan(weights.lm_head, self.xl)
 
         # ---- paged KV pools, sized from what is left of the HBM budget ---------------------------
-        self.block_bytes = 2 * m.num_hidden_layers * m.num_key_value_heads * self.bs * m.head_dim * 2
+        self.block_bytes = 2 * m.num_hidden_layers * (m.num_key_value_heads // tp) * self.bs * m.head_dim * 2
         if e.num_gpu_blocks is not None:
             nb = int(e.num_gpu_blocks)
         else:
@@ -121,7 +136,14 @@ class ModelRunner:
                 raise RuntimeError(f"KV budget {budget / 2**30:.1f} GiB holds {nb} blocks; one sequence of "
                                    f"max_model_len={e.max_model_len} needs {self.MB}")
         self.num_blocks = nb
-        L, Hkv, D = m.num_hidden_layers, m.num_key_value_heads, m.head_dim
+        L, Hkv, D = m.num_hidden_layers, m.num_key_value_heads // tp, m.head_dim
+        if tp > 1 and e.num_gpu_blocks is None:
+            # every rank must own the same number of blocks: the schedulers run in lockstep
+            import torch.distributed as dist
+
+            t_nb = torch.tensor([nb], device=dev)
+            dist.all_reduce(t_nb, op=dist.ReduceOp.MIN, group=self.tp_group)
+            nb = self.num_blocks = int(t_nb.item())
         self.k_cache = torch.zeros(L, nb, Hkv, self.bs, D, dtype=bf, device=dev)
         self.v_cache = torch.zeros(L, nb, Hkv, self.bs, D, dtype=bf, device=dev)
 
@@ -145,28 +167,43 @@ class ModelRunner:
             raise _cabi.AtxError(f"atx error {rc}: {self.lib.atx_last_error().decode()}")
 
     def _forward(self, T: int, n_dec: int, dec_splits: int, n_pf: int, max_q: int, n_rows: int) -> int:
-        """Issue every kernel of one step on the current stream. Returns the launch count."""
+        """Issue every kernel of one step on the current stream. Returns the launch count.
+
+        Tensor parallel (tp > 1, Megatron split: q/k/v/gate/up by output features = heads, o/down by
+        input features): o_proj and down_proj produce PARTIAL sums into `part`; NCCL all-reduces it
+        over NVLink and the next RMSNorm folds it into the residual stream (`h += part`, part cleared).
+        The LM head is vocabulary-parallel: each rank fills its column slice of a zeroed logits buffer
+        and one all-reduce assembles the full rows, so every rank samples the same token."""
         lib, m, w, ck = self.lib, self.m, self.w, self._ck
         st = torch.cuda.current_stream().cuda_stream
         fl = self.flags
-        H, I, V = m.hidden_size, m.intermediate_size, m.vocab_size
-        Hq, Hkv, D = m.num_attention_heads, m.num_key_value_heads, m.head_dim
+        tp = self.tp
+        H, V = m.hidden_size, m.vocab_size
+        D = m.head_dim
+        Hq, Hkv, I = m.num_attention_heads // tp, m.num_key_value_heads // tp, m.intermediate_size // tp
+        q_size, qkv_size = Hq * D, (Hq + 2 * Hkv) * D
         dp = self._dp
         h, xn, qkv, q, attn, act = (t.data_ptr() for t in (self.h, self.xn, self.qkv, self.q, self.attn, self.act))
+        part = self.part.data_ptr() if tp > 1 else None
+        proj_out = part if tp > 1 else h      # where o_proj / down_proj accumulate
         n = 0
         ck(lib.atx_embed_gather(dp["ids"], w.embed.data_ptr(), h, T, H, V, st))
         n += 1
-        sp_qkv = lib.atx_gemm_auto_splits(m.qkv_size, H, T)
-        qb = m.q_size * 2  # bytes per row of q / attn
+        if tp > 1:
+            self.part[:T].zero_()
+        sp_qkv = lib.atx_gemm_auto_splits(qkv_size, H, T)
+        qb = q_size * 2  # bytes per row of q / attn
+        pending = None   # partial buffer waiting to be folded into h by the next norm
         for li, l in enumerate(w.layers):
             p_qkv, p_o, p_gu, p_down = self.plans[li]
             kc, vc = self.k_cache[li].data_ptr(), self.v_cache[li].data_ptr()
             if sp_qkv > 1:
-                ck(lib.atx_rmsnorm(h, None, l.ln1.data_ptr(), xn, T, H, m.rms_norm_eps, qkv, T * m.qkv_size * 4, fl, st))
-                ck(lib.atx_gemm_run(p_qkv._h, qkv, m.qkv_size, T, _cabi.GEMM_ADD_F32, sp_qkv, fl, st))
+                ck(lib.atx_rmsnorm(h, pending, None, l.ln1.data_ptr(), xn, T, H, m.rms_norm_eps, qkv, T * qkv_size * 4,
+                                   fl, st))
+                ck(lib.atx_gemm_run(p_qkv._h, qkv, qkv_size, T, _cabi.GEMM_ADD_F32, sp_qkv, fl, st))
             else:
-                ck(lib.atx_rmsnorm(h, None, l.ln1.data_ptr(), xn, T, H, m.rms_norm_eps, None, 0, fl, st))
-                ck(lib.atx_gemm_run(p_qkv._h, qkv, m.qkv_size, T, _cabi.GEMM_STORE_F32, 1, fl, st))
+                ck(lib.atx_rmsnorm(h, pending, None, l.ln1.data_ptr(), xn, T, H, m.rms_norm_eps, None, 0, fl, st))
+                ck(lib.atx_gemm_run(p_qkv._h, qkv, qkv_size, T, _cabi.GEMM_STORE_F32, 1, fl, st))
             ck(lib.atx_rope_kv_write(qkv, dp["pos"], dp["slots"], self.rope.data_ptr(), q, kc, vc, T, Hq, Hkv, D,
                                      self.bs, fl, st))
             n += 3
@@ -180,19 +217,38 @@ class ModelRunner:
                                               attn + n_dec * qb, n_pf, max_q, Hq, Hkv, D, self.bs, self.MB,
                                               self.scale, fl, st))
                 n += 1
-            ck(lib.atx_gemm_run(p_o._h, h, H, T, _cabi.GEMM_ADD_F32, 0, fl, st))
-            ck(lib.atx_rmsnorm(h, None, l.ln2.data_ptr(), xn, T, H, m.rms_norm_eps, None, 0, fl, st))
+            ck(lib.atx_gemm_run(p_o._h, proj_out, H, T, _cabi.GEMM_ADD_F32, 0, fl, st))
+            if tp > 1:
+                self._all_reduce(self.part[:T])
+                pending = part
+            ck(lib.atx_rmsnorm(h, pending, None, l.ln2.data_ptr(), xn, T, H, m.rms_norm_eps, None, 0, fl, st))
             ck(lib.atx_gemm_run(p_gu._h, act, I, T, _cabi.GEMM_SWIGLU_BF16, 1, fl, st))  # silu(g)*u in the epilogue
-            ck(lib.atx_gemm_run(p_down._h, h, H, T, _cabi.GEMM_ADD_F32, 0, fl, st))
+            ck(lib.atx_gemm_run(p_down._h, proj_out, H, T, _cabi.GEMM_ADD_F32, 0, fl, st))
+            if tp > 1:
+                self._all_reduce(self.part[:T])
             n += 4
         if n_rows:
-            ck(lib.atx_rmsnorm(h, dp["rows"], w.norm.data_ptr(), self.xl.data_ptr(), n_rows, H, m.rms_norm_eps, None,
-                               0, fl, st))
-            ck(lib.atx_gemm_run(self.plan_lm._h, self.logits.data_ptr(), V, n_rows, _cabi.GEMM_STORE_F32, 1, fl, st))
+            ck(lib.atx_rmsnorm(h, pending, dp["rows"], w.norm.data_ptr(), self.xl.data_ptr(), n_rows, H, m.rms_norm_eps,
+                               None, 0, fl, st))
+            if tp > 1:
+                Vl = V // tp
+                self.logits[:n_rows].zero_()
+                ck(lib.atx_gemm_run(self.plan_lm._h, self.logits.data_ptr() + 4 * Vl * self.tp_rank, V, n_rows,
+                                    _cabi.GEMM_STORE_F32, 1, fl, st))
+                self._all_reduce(self.logits[:n_rows])
+            else:
+                ck(lib.atx_gemm_run(self.plan_lm._h, self.logits.data_ptr(), V, n_rows, _cabi.GEMM_STORE_F32, 1, fl,
+                                    st))
             ck(lib.atx_sample(self.logits.data_ptr(), V, dp["temps"], dp["top_p"], dp["seeds"], dp["steps"],
                               self.out_ids.data_ptr(), n_rows, V, fl, st))
             n += 3
         return n
+
+    def _all_reduce(self, t: torch.Tensor) -> None:
+        import torch.distributed as dist
+
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.tp_group)
+        self.allreduce_calls += 1
 
     # ----------------------------------------------------------------------------------------------
     def _h2d(self, name: str, count: int) -> None:
@@ -207,7 +263,7 @@ class ModelRunner:
         if n_dec == 0:
             return 1
         by_len = max(1, (max_len + 63) // 64)
-        by_grid = max(1, (16 * 148) // max(1, n_dec * self.m.num_key_value_heads))
+        by_grid = max(1, (16 * 148) // max(1, n_dec * max(1, self.m.num_key_value_heads // self.tp)))
         s = 1
         while s * 2 <= min(by_len, by_grid, self.max_splits):
             s *= 2

@@ -43,6 +43,7 @@ class ModelWeights:
         self.layers: List[LayerWeights] = []
         self.norm: torch.Tensor = None       # [H] bf16
         self.lm_head: torch.Tensor = None    # [V, H] bf16 (aliases embed when tied)
+        self.tp_size, self.tp_rank = 1, 0
 
     def nbytes(self) -> int:
         seen, total = set(), 0
@@ -61,37 +62,55 @@ class ModelWeights:
 
     # ---- constructors ---------------------------------------------------------------------------
     @classmethod
-    def from_state_dict(cls, cfg: ModelConfig, sd: Dict[str, torch.Tensor], device: torch.device) -> "ModelWeights":
-        """`sd` uses HF names; values may be fp32/bf16 on any device."""
+    def from_state_dict(cls, cfg: ModelConfig, sd: Dict[str, torch.Tensor], device: torch.device, tp_size: int = 1,
+                        tp_rank: int = 0) -> "ModelWeights":
+        """`sd` uses HF names; values may be fp32/bf16 on any device. With tp_size > 1 only this rank's
+        shard is kept (Megatron layout: q/k/v/gate/up split by output rows = heads / features, o/down by
+        input columns, LM head by vocabulary rows; embedding and norms replicated)."""
         w = cls(cfg, device)
+        w.tp_size, w.tp_rank = tp_size, tp_rank
+        r, n = tp_rank, tp_size
 
         def dev(t: torch.Tensor) -> torch.Tensor:
             return t.to(device=device, dtype=torch.bfloat16).contiguous()
+
+        def rows(t: torch.Tensor) -> torch.Tensor:   # output-feature (row) shard
+            k = t.shape[0] // n
+            return t[r * k:(r + 1) * k]
+
+        def cols(t: torch.Tensor) -> torch.Tensor:   # input-feature (column) shard
+            k = t.shape[1] // n
+            return t[:, r * k:(r + 1) * k]
 
         w.embed = dev(sd["model.embed_tokens.weight"])
         for i in range(cfg.num_hidden_layers):
             p = f"model.layers.{i}."
             l = LayerWeights()
             l.ln1 = dev(sd[p + "input_layernorm.weight"])
-            l.wqkv = dev(torch.cat([sd[p + "self_attn.q_proj.weight"], sd[p + "self_attn.k_proj.weight"],
-                                    sd[p + "self_attn.v_proj.weight"]], dim=0))
-            l.wo = dev(sd[p + "self_attn.o_proj.weight"])
+            l.wqkv = dev(torch.cat([rows(sd[p + "self_attn.q_proj.weight"]), rows(sd[p + "self_attn.k_proj.weight"]),
+                                    rows(sd[p + "self_attn.v_proj.weight"])], dim=0))
+            l.wo = dev(cols(sd[p + "self_attn.o_proj.weight"]))
             l.ln2 = dev(sd[p + "post_attention_layernorm.weight"])
-            l.wgu = dev(interleave_gate_up(sd[p + "mlp.gate_proj.weight"], sd[p + "mlp.up_proj.weight"]))
-            l.wdown = dev(sd[p + "mlp.down_proj.weight"])
+            l.wgu = dev(interleave_gate_up(rows(sd[p + "mlp.gate_proj.weight"]), rows(sd[p + "mlp.up_proj.weight"])))
+            l.wdown = dev(cols(sd[p + "mlp.down_proj.weight"]))
             w.layers.append(l)
         w.norm = dev(sd["model.norm.weight"])
-        w.lm_head = w.embed if cfg.tie_word_embeddings or "lm_head.weight" not in sd else dev(sd["lm_head.weight"])
+        head = sd["model.embed_tokens.weight"] if cfg.tie_word_embeddings or "lm_head.weight" not in sd \
+            else sd["lm_head.weight"]
+        w.lm_head = w.embed if (n == 1 and head is sd["model.embed_tokens.weight"]) else dev(rows(head))
         w._check()
         return w
 
     @classmethod
-    def random(cls, cfg: ModelConfig, seed: int, device: torch.device, std: float = 0.02) -> "ModelWeights":
+    def random(cls, cfg: ModelConfig, seed: int, device: torch.device, std: float = 0.02, tp_size: int = 1,
+               tp_rank: int = 0) -> "ModelWeights":
         """Seeded random init generated ON the device (16 GB for 8B in well under a second). Values
-        do not match the CPU-seeded oracle weights; parity tests use from_state_dict instead."""
+        do not match the CPU-seeded oracle weights; parity tests use from_state_dict instead. With
+        tp_size > 1 only a shard-shaped set is generated (70B: 17.4 GB per rank at tp 8)."""
         w = cls(cfg, device)
-        g = torch.Generator(device=device).manual_seed(seed)
-        H, I = cfg.hidden_size, cfg.intermediate_size
+        w.tp_size, w.tp_rank = tp_size, tp_rank
+        g = torch.Generator(device=device).manual_seed(seed * 1000 + tp_rank)
+        H, I = cfg.hidden_size, cfg.intermediate_size // tp_size
 
         def mat(n, k):
             return (torch.randn(n, k, generator=g, device=device, dtype=torch.float32) * std).to(torch.bfloat16)
@@ -102,16 +121,17 @@ class ModelWeights:
         w.embed = mat(cfg.vocab_size, H)
         for _ in range(cfg.num_hidden_layers):
             l = LayerWeights()
-            l.ln1, l.wqkv, l.wo = vec(H), mat(cfg.qkv_size, H), mat(H, cfg.q_size)
+            l.ln1, l.wqkv, l.wo = vec(H), mat(cfg.qkv_size // tp_size, H), mat(H, cfg.q_size // tp_size)
             l.ln2, l.wgu, l.wdown = vec(H), mat(2 * I, H), mat(H, I)
             w.layers.append(l)
         w.norm = vec(H)
-        w.lm_head = w.embed if cfg.tie_word_embeddings else mat(cfg.vocab_size, H)
+        w.lm_head = w.embed if (cfg.tie_word_embeddings and tp_size == 1) else mat(cfg.vocab_size // tp_size, H)
         w._check()
         return w
 
     @classmethod
-    def from_hf_dir(cls, cfg: ModelConfig, path: Path, device: torch.device) -> "ModelWeights":
+    def from_hf_dir(cls, cfg: ModelConfig, path: Path, device: torch.device, tp_size: int = 1,
+                    tp_rank: int = 0) -> "ModelWeights":
         """Load *.safetensors shards of an HF checkpoint directory (hub snapshot layout)."""
         from safetensors import safe_open
 
@@ -123,17 +143,17 @@ class ModelWeights:
             with safe_open(str(f), framework="pt", device="cpu") as sf:
                 for k in sf.keys():
                     sd[k] = sf.get_tensor(k)
-        return cls.from_state_dict(cfg, sd, device)
+        return cls.from_state_dict(cfg, sd, device, tp_size, tp_rank)
 
     def _check(self) -> None:
-        c = self.cfg
+        c, n = self.cfg, self.tp_size
         assert self.embed.shape == (c.vocab_size, c.hidden_size)
-        assert self.lm_head.shape == (c.vocab_size, c.hidden_size)
+        assert self.lm_head.shape == (c.vocab_size // n, c.hidden_size)
         assert len(self.layers) == c.num_hidden_layers
         for l in self.layers:
-            assert l.wqkv.shape == (c.qkv_size, c.hidden_size) and l.wo.shape == (c.hidden_size, c.q_size)
-            assert l.wgu.shape == (2 * c.intermediate_size, c.hidden_size)
-            assert l.wdown.shape == (c.hidden_size, c.intermediate_size)
+            assert l.wqkv.shape == (c.qkv_size // n, c.hidden_size) and l.wo.shape == (c.hidden_size, c.q_size // n)
+            assert l.wgu.shape == (2 * c.intermediate_size // n, c.hidden_size)
+            assert l.wdown.shape == (c.hidden_size, c.intermediate_size // n)
         if c.hidden_size % 64 or c.intermediate_size % 64 or c.q_size % 64:
             raise ValueError("hidden / intermediate / q sizes must be multiples of 64 (GEMM K blocking)")
         if c.head_dim not in (64, 128):

@@ -30,9 +30,9 @@ constexpr int kNormThreads = 256;
 constexpr int kNormMaxVec = 8;  // float4 per thread -> H <= 8192
 
 __global__ void __launch_bounds__(kNormThreads)
-rmsnorm_kernel(const float* __restrict__ x, const int* __restrict__ rows, const uint2* __restrict__ w,
-               uint2* __restrict__ out, int T, int H, float eps, uint4* __restrict__ zero_ptr,
-               long long zero_vecs) {
+rmsnorm_kernel(float* __restrict__ x, float* __restrict__ add, const int* __restrict__ rows,
+               const uint2* __restrict__ w, uint2* __restrict__ out, int T, int H, float eps,
+               uint4* __restrict__ zero_ptr, long long zero_vecs) {
     __shared__ float red[kNormThreads / 32];
     pdl_launch_dependents();
     pdl_wait();
@@ -46,7 +46,8 @@ rmsnorm_kernel(const float* __restrict__ x, const int* __restrict__ rows, const 
     }
     const int t = blockIdx.x;
     const int r = rows ? rows[t] : t;
-    const float4* xr = reinterpret_cast<const float4*>(x + static_cast<long long>(r) * H);
+    float4* xr = reinterpret_cast<float4*>(x + static_cast<long long>(r) * H);
+    float4* ar = add ? reinterpret_cast<float4*>(add + static_cast<long long>(r) * H) : nullptr;
     const int nv = H / 4;
     float4 v[kNormMaxVec];
     float ss = 0.f;
@@ -55,6 +56,16 @@ rmsnorm_kernel(const float* __restrict__ x, const int* __restrict__ rows, const 
         const int i = threadIdx.x + j * kNormThreads;
         if (i < nv) {
             v[j] = xr[i];
+            if (ar) {
+                // tensor-parallel residual: x += (all-reduced partial projection); the partial buffer is
+                // handed back cleared for the next split-K accumulation (not in row-gather mode)
+                const float4 a = ar[i];
+                v[j].x += a.x; v[j].y += a.y; v[j].z += a.z; v[j].w += a.w;
+                if (!rows) {
+                    xr[i] = v[j];
+                    ar[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+            }
             ss += v[j].x * v[j].x + v[j].y * v[j].y + v[j].z * v[j].z + v[j].w * v[j].w;
         }
     }
@@ -180,7 +191,7 @@ int atx_embed_gather(const int* ids, const void* table, float* out, int T, int H
     return ATX_OK;
 }
 
-int atx_rmsnorm(const float* x, const int* rows, const void* w, void* out, int T, int H, float eps,
+int atx_rmsnorm(float* x, float* add, const int* rows, const void* w, void* out, int T, int H, float eps,
                 void* zero_ptr, long long zero_bytes, int flags, atx_stream_t stream) {
     ATX_REQUIRE(x && w && out, "atx_rmsnorm: null pointer");
     ATX_REQUIRE(T > 0 && H > 0 && H % 4 == 0 && H <= kNormThreads * kNormMaxVec * 4,
@@ -196,7 +207,7 @@ int atx_rmsnorm(const float* x, const int* rows, const void* w, void* out, int T
     cfg.blockDim = dim3(kNormThreads);
     cfg.stream = reinterpret_cast<cudaStream_t>(stream);
     set_pdl(cfg, attr, flags);
-    ATX_CUDA(cudaLaunchKernelEx(&cfg, rmsnorm_kernel, x, rows, reinterpret_cast<const uint2*>(w),
+    ATX_CUDA(cudaLaunchKernelEx(&cfg, rmsnorm_kernel, x, add, rows, reinterpret_cast<const uint2*>(w),
                                 reinterpret_cast<uint2*>(out), T, H, eps, reinterpret_cast<uint4*>(zero_ptr), zv));
     return ATX_OK;
 }

@@ -69,10 +69,12 @@ int atx_embed_gather(const int* ids, const void* table, float* out, int T, int H
                      atx_stream_t stream);
 
 /* ---- RMSNorm: out[t, :] = bf16( w * x[r, :] * rsqrt(mean(x[r, :]^2) + eps) ), r = rows ? rows[t] : t
- * Replaces LlamaRMSNorm.forward (modeling_llama.py:62-67). x fp32 (the residual stream), w bf16,
- * out bf16. Optionally zero-fills `zero_ptr[0 .. zero_bytes)` (16-byte multiple) for a following
- * split-K GEMM, saving a memset node. */
-int atx_rmsnorm(const float* x, const int* rows, const void* w, void* out, int T, int H, float eps,
+ * Replaces LlamaRMSNorm.forward (modeling_llama.py:62-67) and, with `add`, the residual add before it
+ * (LlamaDecoderLayer.forward :313-332). x fp32 (the residual stream), w bf16, out bf16.
+ * add (nullable, fp32 [T, H]): x[r, :] += add[r, :] first; without `rows` the sum is written back to x
+ * and add is cleared (tensor parallelism: add = all-reduced partial o_proj / down_proj output).
+ * Optionally zero-fills `zero_ptr[0 .. zero_bytes)` (16-byte multiple) for a following split-K GEMM. */
+int atx_rmsnorm(float* x, float* add, const int* rows, const void* w, void* out, int T, int H, float eps,
                 void* zero_ptr, long long zero_bytes, int flags, atx_stream_t stream);
 
 /* ---- RoPE + KV-cache write ------------------------------------------------------------------------

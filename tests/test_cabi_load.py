@@ -38,7 +38,7 @@ def test_version_and_argument_errors_without_gpu(lib):
     h = ctypes.c_void_p()
     rc = lib.atx_gemm_plan_create(ctypes.byref(h), None, 128, 64, None, 8, 64)
     assert rc == -1 and b"null pointer" in lib.atx_last_error()
-    rc = lib.atx_rmsnorm(None, None, None, None, 4, 64, 1e-5, None, 0, 0, None)
+    rc = lib.atx_rmsnorm(None, None, None, None, None, 4, 64, 1e-5, None, 0, 0, None)
     assert rc == -1 and b"atx_rmsnorm" in lib.atx_last_error()
     assert lib.atx_paged_attn_decode_workspace_bytes(6, 32, 128, 4) == 6 * 32 * 4 * 130 * 4
     assert lib.atx_paged_attn_decode_workspace_bytes(6, 32, 128, 1) == 0
