@@ -284,7 +284,8 @@ class ModelRunner:
             return {}
         if T_real > self.Tmax or n_dec + n_pf > self.Smax:
             raise RuntimeError("step exceeds the runner's static capacity")
-        use_graph = self.e.enable_cuda_graphs and n_pf == 0 and _bucket(n_dec, _GRAPH_BUCKETS) is not None \
+        # TP steps contain NCCL all-reduces; their capture hung on this stack (r01), so TP runs eagerly
+        use_graph = self.e.enable_cuda_graphs and self.tp == 1 and n_pf == 0 and _bucket(n_dec, _GRAPH_BUCKETS) is not None \
             and _bucket(n_dec, _GRAPH_BUCKETS) <= self.Smax
         B = _bucket(n_dec, _GRAPH_BUCKETS) if use_graph else n_dec
         T = B + (T_real - n_dec)
