@@ -263,6 +263,175 @@ def cpu_reference_sample(threads: int, prompt_len: int = 64, new_tokens: int = 4
 
 
 # ------------------------------------------------------------------------------------------------------
+def run_other_workload(args, rank, world, local):
+    """BASELINE.json configs[2..4]: opt-in workloads (`--workload trace|long|tp70b`). Each prints one JSON
+    line of the same shape as the headline run (value = aggregate output tokens/s)."""
+    import torch
+
+    from atx.config import EngineConfig, ModelSource, model_config_by_name
+    from atx.engine import AsyncEngine, LLMEngine
+    from atx.scheduler import SamplingParams
+
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    pk = peaks()
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    out = {"metric": METRIC, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+           "higher_is_better": True, "vs_baseline": None, "dtype": "bf16", "data": "synthetic"}
+    if args.workload == "trace":
+        from atx import trace as TR
+
+        mcfg = model_config_by_name("8b")
+        ecfg = EngineConfig(max_model_len=8192, max_num_seqs=32, max_num_batched_tokens=8192,
+                            gpu_memory_utilization=0.90, device=local)
+        engine = LLMEngine(ModelSource(mcfg, None, 0), ecfg)
+        aeng = AsyncEngine(engine)
+        tasks_per_gpu = 4
+
+        def one(step):
+            tasks = TR.generate_tasks(tasks_per_gpu, seed=3 + 100 * step + rank)
+            t0 = time.perf_counter()
+            recs = asyncio.run(TR.replay(aeng, tasks, seed=3 + step, id_prefix=f"s{step}r{rank}-"))
+            return recs, time.perf_counter() - t0
+        for w in range(args.warmup):
+            one(-1 - w + 1000)
+        barrier()
+        l0 = engine.runner.kernel_launches
+        t0 = time.perf_counter()
+        recs = []
+        for k in range(args.steps):
+            r_, _ = one(k)
+            recs += r_
+        barrier()
+        wall = max_over_ranks(dist, [time.perf_counter() - t0], "cuda")[0]
+        summ = TR.summarize(recs, wall)
+        toks = sum(gather_over_ranks(dist, [summ["output_tokens"]], world))
+        ttft = gather_over_ranks(dist, [r.ttft_s for r in recs], world)
+        aeng.shutdown()
+        if rank == 0 and args.trace_out:
+            TR.write_reference_formats(recs, Path(args.trace_out))
+        out.update({"value": round(toks / wall, 1), "ms_per_step": round(1e3 * wall / args.steps, 2), "scaling": "weak",
+                    "ttft_p50_ms": round(1e3 * statistics.median(ttft), 2),
+                    "gpu_launches": engine.runner.kernel_launches - l0,
+                    "config": {"workload": "BASELINE configs[2]: Llama-3.1-8B data-parallel replicas replaying synthetic "
+                                           "AgentVerse workflows (recruitment -> decision rounds -> N<=5 concurrent "
+                                           "executions -> evaluation -> final), 4 concurrent tasks per GPU, closed loop, "
+                                           "5-20 ms think time, seeded generator atx/trace.py (the reference ships no traces)",
+                               "parallelism": f"dp{world}", "requests": summ["requests"] * world,
+                               "prompt_tokens": summ["prompt_tokens"], "cached_prompt_tokens": summ["cached_prompt_tokens"]}})
+    elif args.workload == "long":
+        mcfg = model_config_by_name("8b")
+        B, P, O = 16, 32768, args.long_out
+        ecfg = EngineConfig(max_model_len=P + O + 16, max_num_seqs=B, max_num_batched_tokens=8192,
+                            gpu_memory_utilization=0.92, enable_prefix_caching=False, device=local)
+        engine = LLMEngine(ModelSource(mcfg, None, 0), ecfg)
+        r = engine.runner
+        import numpy as np
+
+        def one(step):
+            rng = np.random.default_rng(5 + step)
+            prompts = [rng.integers(0, 128000, P).tolist() for _ in range(B)]
+            params = SamplingParams(temperature=0.0, max_tokens=O, ignore_eos=True)
+            r.step_events = []
+            t0 = time.perf_counter()
+            seqs = [engine.add_request(f"l{step}-{i}", p, params) for i, p in enumerate(prompts)]
+            while engine.has_work():
+                engine.step()
+            torch.cuda.synchronize()
+            ev, r.step_events = r.step_events, None
+            return seqs, ev, time.perf_counter() - t0
+        for w in range(args.warmup):
+            one(1000 + w)
+        walls, evs = [], []
+        for k in range(args.steps):
+            seqs, ev, wall = one(k)
+            walls.append(wall)
+            evs += ev
+        dec = [(a.elapsed_time(b), ctx) for (a, b, nd, npf, ctx) in evs if npf == 0 and nd == B]
+        pf = [(a.elapsed_time(b), npf) for (a, b, nd, npf, ctx) in evs if npf > 0]
+        ms = sum(d[0] for d in dec) / len(dec)
+        byts = mcfg.weight_bytes_per_decode_step() + mcfg.kv_bytes_per_token() * (sum(d[1] for d in dec) / len(dec))
+        pf_ms = sum(p[0] for p in pf) / args.steps
+        flops = 2 * 7.50e9 * B * P + 2 * P * P * mcfg.hidden_size * mcfg.num_hidden_layers * B  # SURVEY 8d
+        wall = sum(walls) / len(walls)
+        out.update({"value": round(B * O / wall, 2), "ms_per_step": round(1e3 * wall, 1), "scaling": "weak",
+                    "ttft_p50_ms": round(1e3 * statistics.median(s.first_token_time - s.arrival for s in seqs), 1),
+                    "decode_step": {"ms": round(ms, 3), "algorithmic_bytes": round(byts),
+                                    "achieved": round(byts / ms / 1e6, 1), "peak": pk["hbm_gbs"], "unit": "GB/s",
+                                    "frac": round(byts / ms / 1e6 / pk["hbm_gbs"], 4),
+                                    "decode_tokens_per_s": round(B / ms * 1e3, 1)},
+                    "prefill": {"ms": round(pf_ms, 1), "tokens": B * P, "tokens_per_s": round(B * P / pf_ms * 1e3),
+                                "tflops": round(flops / pf_ms / 1e9, 1)},
+                    "gpu_launches": r.kernel_launches,
+                    "config": {"workload": f"BASELINE configs[4]: Llama-3.1-8B long-context, batch {B} x {P}-token prompts "
+                                           f"(chunked prefill, 8192-token budget) + {O} greedy tokens over paged KV",
+                               "parallelism": "1 GPU", "kv_blocks": r.num_blocks}})
+    elif args.workload == "tp70b":
+        mcfg = model_config_by_name("70b", args.layers)
+        B, P, O = 32, 1024, args.tp_out
+        ecfg = EngineConfig(max_model_len=4096, max_num_seqs=B, max_num_batched_tokens=8192, gpu_memory_utilization=0.90,
+                            device=local, tp_size=world, tp_rank=rank)
+        engine = LLMEngine(ModelSource(mcfg, None, 0), ecfg)
+        r = engine.runner
+        import numpy as np
+
+        def one(step):
+            rng = np.random.default_rng(4 + step)     # identical on every rank: schedulers run in lockstep
+            shared = rng.integers(0, 128000, SHARED).tolist()
+            prompts = [shared + rng.integers(0, 128000, P - SHARED).tolist() for _ in range(B)]
+            params = SamplingParams(temperature=0.0, max_tokens=O, ignore_eos=True)
+            r.step_events = []
+            seqs = [engine.add_request(f"t{step}-{i}", p, params) for i, p in enumerate(prompts)]
+            t = time.monotonic()
+            for s_ in seqs:
+                s_.arrival = t
+            while engine.has_work():
+                engine.step()
+            ev, r.step_events = r.step_events, None
+            return seqs, ev
+        for w in range(args.warmup):
+            one(1000 + w)
+        barrier()
+        t0 = time.perf_counter()
+        evs, ttfts = [], []
+        for k in range(args.steps):
+            seqs, ev = one(k)
+            evs += ev
+            ttfts += [s.first_token_time - s.arrival for s in seqs]
+        barrier()
+        wall = max_over_ranks(dist, [time.perf_counter() - t0], "cuda")[0]
+        dec = [(a.elapsed_time(b), ctx) for (a, b, nd, npf, ctx) in evs if npf == 0 and nd == B]
+        ms = sum(d[0] for d in dec) / len(dec)
+        byts = (mcfg.weight_bytes_per_decode_step() + mcfg.kv_bytes_per_token() * (sum(d[1] for d in dec) / len(dec))) / world
+        out.update({"value": round(args.steps * B * O / wall, 1), "ms_per_step": round(1e3 * wall / args.steps, 1),
+                    "scaling": "strong", "ttft_p50_ms": round(1e3 * statistics.median(ttfts), 1),
+                    "decode_step": {"ms": round(ms, 3), "algorithmic_bytes_per_gpu": round(byts),
+                                    "achieved": round(byts / ms / 1e6, 1), "peak": pk["hbm_gbs"], "unit": "GB/s per GPU",
+                                    "frac": round(byts / ms / 1e6 / pk["hbm_gbs"], 4),
+                                    "decode_tokens_per_s": round(B / ms * 1e3, 1),
+                                    "allreduces_per_step": 2 * mcfg.num_hidden_layers + 1,
+                                    "allreduce_message_bytes": B * mcfg.hidden_size * 4},
+                    "gpu_launches": r.kernel_launches,
+                    "config": {"workload": f"BASELINE configs[3]: Llama-3.1-70B ({mcfg.num_hidden_layers} layers) tensor-"
+                                           f"parallel TP={world}, NCCL all-reduce over NVLink, agent fan-out batch {B}, "
+                                           f"{P}-token prompts (768 shared), {O} greedy tokens; eager launches (no CUDA "
+                                           "graph under TP yet)",
+                               "parallelism": f"tp{world}"}})
+    if rank == 0:
+        print(json.dumps(out))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
 def main() -> None:
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -273,6 +442,12 @@ def main() -> None:
     ap.add_argument("--no-prefix-cache", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--workload", default="fanout", choices=["fanout", "trace", "long", "tp70b"],
+                    help="fanout = headline BASELINE configs[1] (default); the others are configs[2..4]")
+    ap.add_argument("--trace-out", default="", help="directory for response.json / llm_calls.jsonl of a trace replay")
+    ap.add_argument("--long-out", type=int, default=128)
+    ap.add_argument("--tp-out", type=int, default=256)
+    ap.add_argument("--layers", type=int, default=None, help="tp70b only: reduce depth for smoke runs")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -292,6 +467,10 @@ def main() -> None:
             "cpu_baseline": best,
             "e2e": {"value": best["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         }))
+        return
+
+    if args.workload != "fanout":
+        run_other_workload(args, rank, world, local)
         return
 
     import torch
