@@ -165,7 +165,9 @@ class B200Backend:
                            request_id: Optional[str] = None, log_progress: bool = True,
                            max_tokens: Optional[int] = None, temperature: Optional[float] = None,
                            top_p: Optional[float] = None, seed: Optional[int] = None,
-                           ignore_eos: Optional[bool] = None) -> Generation:
+                           ignore_eos: Optional[bool] = None, on_text=None) -> Generation:
+        """`on_text(delta: str)` (optional, may be a coroutine function) receives the newly decoded text
+        after every engine step: the hook behind `"stream": true`."""
         from atx.scheduler import SamplingParams
 
         if request_id is None:
@@ -189,6 +191,7 @@ class B200Backend:
         gen_span = None
         gen_start = None
         final = None
+        sent = 0
         try:
             async for out in self._engine.generate(list(prompt_ids), params, request_id):
                 now = time.monotonic()
@@ -203,6 +206,15 @@ class B200Backend:
                         gen_span.set_attribute("app.request_id", request_id)
                     gen_start = now
                 final = out
+                if on_text is not None:
+                    full = self._tokenizer.decode(list(out.token_ids), skip_special_tokens=True)
+                    if full.endswith("\ufffd") and not out.finished:
+                        full = full.rstrip("\ufffd")   # hold back an incomplete multi-byte character
+                    if len(full) > sent:
+                        res = on_text(full[sent:])
+                        if hasattr(res, "__await__"):
+                            await res
+                        sent = len(full)
                 if log_progress and now - last_log >= 2.0:
                     n = len(out.token_ids)
                     print(f"[llm] req={request_id} PROGRESS tokens={n} speed={n / max(now - t0, 1e-9):.1f} tok/s",

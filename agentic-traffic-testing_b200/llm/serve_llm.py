@@ -14,7 +14,9 @@ Contract kept byte-for-byte where clients depend on it (reference llm/serve_llm.
              --max-num-batched-tokens --gpu-memory-utilization, env fallbacks with CLI winning    (:1049-1104)
   log lines  [llm] req=<id> START|PROGRESS|GENERATED|DONE|ERROR|PROMPT_TRUNCATED ...
 
-Additions (none changes the above): `max_new_tokens` alias of the HF server (hf_cpu_server.py:81),
+Additions (none changes the above): `"stream": true` on /chat answers as server-sent events
+(`data: {"delta": str}` per engine step, then `data: {"output", "meta"}` and `data: [DONE]`; SURVEY.md
+section 8 row f4); `max_new_tokens` alias of the HF server (hf_cpu_server.py:81),
 native OpenAI-style /v1/chat/completions, /v1/completions, /v1/models (llm/openai_api.py), exact
 token counts in `meta`, the llm_batch_size histogram is actually observed.
 The engine beneath is the atx scheduler + sm_100a kernels; there is no vLLM and no CPU fallback.
@@ -176,7 +178,7 @@ async def handle_metrics(request: web.Request) -> web.Response:
 
 async def run_generation(request: web.Request, span: Any, *, prompt: str, original_prompt: str,
                          max_tokens: Optional[int], request_id: str, templated: bool, inflight_now: int,
-                         sampling: Optional[dict] = None):
+                         sampling: Optional[dict] = None, on_text=None):
     """Shared tail of /chat and the OpenAI routes: truncation, span attributes, logging, generation,
     metrics. Returns (Generation | None, latency_s, error text | None)."""
     start = request["t_start"]
@@ -195,8 +197,11 @@ async def run_generation(request: web.Request, span: Any, *, prompt: str, origin
           flush=True)
     try:
         if hasattr(_backend, "generate_ids"):
+            extra = dict(sampling or {})
+            if on_text is not None:
+                extra["on_text"] = on_text
             gen = await _backend.generate_ids(prompt_ids, prompt=prompt, request_id=request_id, log_progress=True,
-                                              max_tokens=max_tokens, **(sampling or {}))
+                                              max_tokens=max_tokens, **extra)
             p_tok, c_tok = gen.prompt_tokens, len(gen.token_ids)
             if not LLM_METRICS_INCLUDE_TOKENS:
                 p_tok = c_tok = None
@@ -262,11 +267,24 @@ async def handle_chat(request: web.Request) -> web.Response:
 
             skip_template = bool(data.get("skip_chat_template", False))
             formatted = prompt if skip_template else _backend.apply_chat_template(prompt, data.get("system_prompt"))
+            sse: Optional[web.StreamResponse] = None
+            on_text = None
+            if data.get("stream") is True and hasattr(_backend, "generate_ids"):
+                sse = web.StreamResponse(headers={"Content-Type": "text/event-stream", "Cache-Control": "no-cache",
+                                                  "X-Request-ID": request_id})
+                await sse.prepare(request)
+
+                async def on_text(delta: str) -> None:
+                    await sse.write(b"data: " + json.dumps({"delta": delta}).encode() + b"\n\n")
             gen, latency_s, err, p_tok, c_tok = await run_generation(
                 request, span, prompt=formatted, original_prompt=prompt, max_tokens=max_tokens,
                 request_id=request_id, templated=(not skip_template) and LLM_APPLY_CHAT_TEMPLATE,
-                inflight_now=inflight_now)
+                inflight_now=inflight_now, on_text=on_text)
             if err is not None:
+                if sse is not None:
+                    await sse.write(b"data: " + json.dumps({"error": f"Generation failed: {err}"}).encode() + b"\n\n")
+                    await sse.write_eof()
+                    return sse
                 return web.json_response({"error": f"Generation failed: {err}"}, status=500)
             meta = {
                 "request_id": request_id,
@@ -277,6 +295,11 @@ async def handle_chat(request: web.Request) -> web.Response:
                 "total_tokens": (p_tok + c_tok) if (p_tok is not None and c_tok is not None) else None,
                 "otel": _otel_span_metadata(span),
             }
+            if sse is not None:
+                await sse.write(b"data: " + json.dumps({"output": gen.text, "meta": meta}).encode() + b"\n\n")
+                await sse.write(b"data: [DONE]\n\n")
+                await sse.write_eof()
+                return sse
             return web.json_response({"output": gen.text, "meta": meta})
 
 

@@ -195,6 +195,22 @@ def test_openai_chat_completions_shape(served):
     assert st == 200 and body["object"] == "text_completion" and tok.decode(eng.seen[-1]["ids"]) == "abc"
 
 
+def test_chat_streaming_sse(served):
+    S, eng, client, loop = served
+
+    async def go():
+        r = await client.post("/chat", json={"prompt": "hello", "max_tokens": 4, "stream": True})
+        assert r.status == 200 and r.headers["Content-Type"].startswith("text/event-stream")
+        return (await r.read()).decode()
+    body = loop.run_until_complete(go())
+    events = [e[len("data: "):] for e in body.strip().split("\n\n")]
+    assert events[-1] == "[DONE]"
+    deltas = [json.loads(e)["delta"] for e in events[:-2]]
+    final = json.loads(events[-2])
+    assert len(deltas) == 4 and "".join(deltas) == final["output"]
+    assert final["meta"]["completion_tokens"] == 4 and S._Traffic.inflight == 0
+
+
 def test_cli_and_env_precedence(monkeypatch):
     from llm import serve_llm as S
 
