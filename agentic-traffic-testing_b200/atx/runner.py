@@ -285,7 +285,8 @@ class ModelRunner:
         if T_real > self.Tmax or n_dec + n_pf > self.Smax:
             raise RuntimeError("step exceeds the runner's static capacity")
         # TP steps contain NCCL all-reduces; their capture hung on this stack (r01), so TP runs eagerly
-        use_graph = self.e.enable_cuda_graphs and self.tp == 1 and n_pf == 0 and _bucket(n_dec, _GRAPH_BUCKETS) is not None \
+        use_graph = self.e.enable_cuda_graphs and (self.tp == 1 or os.environ.get("ATX_TP_GRAPHS") == "1") \
+            and n_pf == 0 and _bucket(n_dec, _GRAPH_BUCKETS) is not None \
             and _bucket(n_dec, _GRAPH_BUCKETS) <= self.Smax
         B = _bucket(n_dec, _GRAPH_BUCKETS) if use_graph else n_dec
         T = B + (T_real - n_dec)
@@ -402,7 +403,7 @@ class ModelRunner:
         torch.cuda.current_stream().wait_stream(s)
         torch.cuda.synchronize(self.dev)
         g = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(g, stream=s):
+        with torch.cuda.graph(g, stream=s, capture_error_mode="thread_local"):
             n = self._forward(B, B, splits, 0, 0, B)
         self._graphs[(B, splits)] = g
         self._graph_launches[(B, splits)] = n
