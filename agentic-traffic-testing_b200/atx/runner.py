@@ -409,6 +409,13 @@ class ModelRunner:
         self._graph_launches[(B, splits)] = n
         return g
 
+    def close(self) -> None:
+        """Drop captured graphs (they pin NCCL work under TP: destroying the process group while they
+        are alive dead-locks at exit) and drain the stream."""
+        self._graphs.clear()
+        self._graph_launches.clear()
+        torch.cuda.synchronize(self.dev)
+
     # ---- capacity facts for the server's gauges ---------------------------------------------------
     def kv_cache_info(self) -> Tuple[int, int]:
         return self.num_blocks, self.bs

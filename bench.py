@@ -428,7 +428,8 @@ def run_other_workload(args, rank, world, local):
                                            "graph under TP yet)",
                                "parallelism": f"tp{world}"}})
     if rank == 0:
-        print(json.dumps(out))
+        print(json.dumps(out), flush=True)
+    engine.runner.close()
     if dist is not None:
         dist.destroy_process_group()
 

@@ -43,6 +43,7 @@ def _rank(rank, world, port, graphs, q):
         while eng.has_work():
             eng.step()
         q.put((rank, float(np.abs(first - g["logits_last"]).max()), seq.output_ids, eng.runner.allreduce_calls))
+        eng.runner.close()
     finally:
         dist.destroy_process_group()
 
