@@ -151,6 +151,8 @@ class AsyncEngine:
             self._stop = True
             self._cv.notify()
         self._thread.join(timeout=10)
+        if not self._thread.is_alive():
+            self.engine.runner.close()
 
     # ---- facts the HTTP layer exports ---------------------------------------------------------------
     @property

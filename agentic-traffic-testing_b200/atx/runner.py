@@ -284,8 +284,9 @@ class ModelRunner:
             return {}
         if T_real > self.Tmax or n_dec + n_pf > self.Smax:
             raise RuntimeError("step exceeds the runner's static capacity")
-        # TP steps contain NCCL all-reduces; their capture hung on this stack (r01), so TP runs eagerly
-        use_graph = self.e.enable_cuda_graphs and (self.tp == 1 or os.environ.get("ATX_TP_GRAPHS") == "1") \
+        # TP steps contain NCCL all-reduces: they capture fine (thread-local capture mode), but the graphs
+        # must be dropped before the process group is destroyed (close()). ATX_TP_GRAPHS=0 opts out.
+        use_graph = self.e.enable_cuda_graphs and (self.tp == 1 or os.environ.get("ATX_TP_GRAPHS", "1") != "0") \
             and n_pf == 0 and _bucket(n_dec, _GRAPH_BUCKETS) is not None \
             and _bucket(n_dec, _GRAPH_BUCKETS) <= self.Smax
         B = _bucket(n_dec, _GRAPH_BUCKETS) if use_graph else n_dec

@@ -424,8 +424,8 @@ def run_other_workload(args, rank, world, local):
                     "gpu_launches": r.kernel_launches,
                     "config": {"workload": f"BASELINE configs[3]: Llama-3.1-70B ({mcfg.num_hidden_layers} layers) tensor-"
                                            f"parallel TP={world}, NCCL all-reduce over NVLink, agent fan-out batch {B}, "
-                                           f"{P}-token prompts (768 shared), {O} greedy tokens; eager launches (no CUDA "
-                                           "graph under TP yet)",
+                                           f"{P}-token prompts (768 shared), {O} greedy tokens; decode steps replayed as CUDA graphs "
+                                           "with the NCCL all-reduces captured",
                                "parallelism": f"tp{world}"}})
     if rank == 0:
         print(json.dumps(out), flush=True)

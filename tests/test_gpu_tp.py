@@ -48,7 +48,7 @@ def _rank(rank, world, port, graphs, q):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("graphs", [False] + ([True] if os.environ.get("ATX_TP_GRAPHS") == "1" else []))
+@pytest.mark.parametrize("graphs", [False, True])
 def test_tp2_matches_hf_golden(graphs):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
