@@ -30,6 +30,8 @@ sys.path.insert(0, str(ROOT / "agentic-traffic-testing_b200"))
 sys.path.insert(0, str(ROOT))
 os.environ.setdefault("LLM_OTEL_EXPORT", "0")
 os.environ.setdefault("LLM_IGNORE_EOS", "1")
+if os.environ.get("ATX_KEEP_NCCL_DEBUG") != "1":
+    os.environ["NCCL_DEBUG"] = "WARN"  # NCCL prints its version banner on stdout otherwise; stdout carries one JSON line
 
 METRIC = "Llama-3.1-8B decode tokens/s + p50 TTFT under agent fan-out"
 UNIT = "tokens/s"
