@@ -153,6 +153,9 @@ class ModelRunner:
         self._h2d_done = torch.cuda.Event()
         self.flags = _cabi.FLAG_PDL if e.use_pdl else 0
         self.lib.atx_gemm_set_l2_prefetch(int(os.environ.get("ATX_L2_PREFETCH_KB", "0")))
+        # o_proj waits behind rope + attention: let its CTAs pull their weight slices into L2 meanwhile
+        self._ablate = set(filter(None, os.environ.get("ATX_ABLATE", "").split(",")))
+        self.o_prefetch = (int(os.environ.get("ATX_O_PREFETCH_KB", "0")) & 0xff) << 8
         self.scale = float(m.head_dim) ** -0.5
         self.launches_last_step = 0
         self.kernel_launches = 0  # cumulative count of our kernels launched (graph replays included)
@@ -187,6 +190,7 @@ class ModelRunner:
         part = self.part.data_ptr() if tp > 1 else None
         proj_out = part if tp > 1 else h      # where o_proj / down_proj accumulate
         n = 0
+        abl = self._ablate  # timing studies only (ATX_ABLATE=attn,rope,norm,reduce): skipped kernels => wrong results
         ck(lib.atx_embed_gather(dp["ids"], w.embed.data_ptr(), h, T, H, V, st))
         n += 1
         if tp > 1:
@@ -197,31 +201,37 @@ class ModelRunner:
         for li, l in enumerate(w.layers):
             p_qkv, p_o, p_gu, p_down = self.plans[li]
             kc, vc = self.k_cache[li].data_ptr(), self.v_cache[li].data_ptr()
-            if sp_qkv > 1:
+            if "norm" in abl:
+                pass
+            elif sp_qkv > 1:
                 ck(lib.atx_rmsnorm(h, pending, None, l.ln1.data_ptr(), xn, T, H, m.rms_norm_eps, qkv, T * qkv_size * 4,
                                    fl, st))
                 ck(lib.atx_gemm_run(p_qkv._h, qkv, qkv_size, T, _cabi.GEMM_ADD_F32, sp_qkv, fl, st))
             else:
                 ck(lib.atx_rmsnorm(h, pending, None, l.ln1.data_ptr(), xn, T, H, m.rms_norm_eps, None, 0, fl, st))
                 ck(lib.atx_gemm_run(p_qkv._h, qkv, qkv_size, T, _cabi.GEMM_STORE_F32, 1, fl, st))
-            ck(lib.atx_rope_kv_write(qkv, dp["pos"], dp["slots"], self.rope.data_ptr(), q, kc, vc, T, Hq, Hkv, D,
+            if "norm" in abl:
+                ck(lib.atx_gemm_run(p_qkv._h, qkv, qkv_size, T, _cabi.GEMM_ADD_F32, sp_qkv, fl, st))
+            if "rope" not in abl:
+              ck(lib.atx_rope_kv_write(qkv, dp["pos"], dp["slots"], self.rope.data_ptr(), q, kc, vc, T, Hq, Hkv, D,
                                      self.bs, fl, st))
             n += 3
-            if n_dec:
+            if n_dec and "attn" not in abl:
                 ck(lib.atx_paged_attn_decode(q, kc, vc, dp["dec_bt"], dp["dec_lens"], attn, self.ws.data_ptr(),
-                                             self.ws.numel() * 4, n_dec, Hq, Hkv, D, self.bs, self.MB, dec_splits,
-                                             self.scale, fl, st))
+                                             self.ws.numel() * 4, n_dec, Hq, Hkv, D, self.bs, self.MB,
+                                             1 if "reduce" in abl else dec_splits, self.scale, fl, st))
                 n += 2 if dec_splits > 1 else 1
             if n_pf:
                 ck(lib.atx_paged_attn_prefill(q + n_dec * qb, kc, vc, dp["pf_bt"], dp["pf_cu"], dp["pf_ctx"],
                                               attn + n_dec * qb, n_pf, max_q, Hq, Hkv, D, self.bs, self.MB,
                                               self.scale, fl, st))
                 n += 1
-            ck(lib.atx_gemm_run(p_o._h, proj_out, H, T, _cabi.GEMM_ADD_F32, 0, fl, st))
+            ck(lib.atx_gemm_run(p_o._h, proj_out, H, T, _cabi.GEMM_ADD_F32, 0, fl | self.o_prefetch, st))
             if tp > 1:
                 self._all_reduce(self.part[:T])
                 pending = part
-            ck(lib.atx_rmsnorm(h, pending, None, l.ln2.data_ptr(), xn, T, H, m.rms_norm_eps, None, 0, fl, st))
+            if "norm" not in abl:
+                ck(lib.atx_rmsnorm(h, pending, None, l.ln2.data_ptr(), xn, T, H, m.rms_norm_eps, None, 0, fl, st))
             ck(lib.atx_gemm_run(p_gu._h, act, I, T, _cabi.GEMM_SWIGLU_BF16, 1, fl, st))  # silu(g)*u in the epilogue
             ck(lib.atx_gemm_run(p_down._h, proj_out, H, T, _cabi.GEMM_ADD_F32, 0, fl, st))
             if tp > 1:

@@ -12,6 +12,7 @@
 // attn_decode_reduce_kernel.
 #include "common.cuh"
 
+#include <cstdlib>
 #include <mutex>
 
 #include "../../include/atx_b200.h"
@@ -270,7 +271,6 @@ attn_decode_mma_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16*
     __shared__ __align__(128) uint8_t smem[kMmaStages * 2 * TILE_BYTES];
 
     pdl_launch_dependents();
-    pdl_wait();
     const int g = blockIdx.x, b = blockIdx.y, sp = blockIdx.z;
     const int lane = threadIdx.x;
     const int gid = lane >> 2, tig = lane & 3;
@@ -299,8 +299,18 @@ attn_decode_mma_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16*
             dec_cp_async16(sv + so, v_cache + base + r * D + c * 8, valid);
         }
     };
-#pragma unroll
-    for (int t = 0; t < kMmaStages - 1; ++t) {
+    // Sequence lengths, block tables and every K/V row except the one written by this step's
+    // rope_kv_write (always in the last tile of the sequence) do not depend on the upstream kernel:
+    // those tiles are requested BEFORE griddepcontrol.wait. Commit groups stay in tile order.
+    const int fresh_tile = (end == L && n_tiles > 0) ? n_tiles - 1 : -1;
+    int t_pre = 0;
+    for (; t_pre < kMmaStages - 1; ++t_pre) {
+        if (t_pre >= n_tiles || t_pre == fresh_tile) break;
+        issue_tile(t_pre);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    pdl_wait();
+    for (int t = t_pre; t < kMmaStages - 1; ++t) {
         if (t < n_tiles) issue_tile(t);
         asm volatile("cp.async.commit_group;" ::: "memory");
     }
@@ -402,6 +412,199 @@ attn_decode_mma_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16*
     }
 }
 
+// ---- cluster variant: the KV splits of one (sequence, KV head) form a thread-block CLUSTER ------------
+// Short-context decode attention is a latency chain, not a bandwidth problem (in-graph ablation: 9 us
+// per layer against 4 us of HBM time), so this variant removes links from the chain:
+//   * everything that does not depend on the upstream kernel is issued BEFORE griddepcontrol.wait:
+//     sequence length, block-table lookups and the cp.async of every K/V tile except the one that
+//     holds the token written by this step's rope_kv_write (always the last tile of the sequence);
+//   * the per-split partials never touch global memory and there is no second kernel: each CTA parks
+//     (m, l, o) in its shared memory, one barrier.cluster, then CTA r merges slice r of the output by
+//     reading its peers through distributed shared memory (mapa + ld.shared::cluster).
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ float dsmem_ld_f32(const float* local_ptr, uint32_t cta) {
+    uint32_t remote;
+    float v;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(smem_u32(local_ptr)), "r"(cta));
+    asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(remote) : "memory");
+    return v;
+}
+
+constexpr int kClStages = 4;  // 3 of the ~5 tiles of a 72-token split are in flight before the wait
+
+template <int D>
+__global__ void __launch_bounds__(32)
+attn_decode_cluster_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __restrict__ k_cache,
+                           const __nv_bfloat16* __restrict__ v_cache, const int* __restrict__ block_table,
+                           const int* __restrict__ seq_lens, __nv_bfloat16* __restrict__ out, int Hq, int Hkv,
+                           int block_size, int max_blocks, int num_splits, float scale_log2, int early_prefetch) {
+    constexpr int CH = D / 8;
+    constexpr int TILE_BYTES = kMmaTile * D * 2;
+    constexpr int kRedFloats = 8 * (D + 2);  // up to 8 heads: o[G][D], m[G], l[G]
+    __shared__ __align__(128) uint8_t smem[kClStages * 2 * TILE_BYTES];
+    __shared__ float red[kRedFloats];
+
+    pdl_launch_dependents();
+    if (!early_prefetch) pdl_wait();
+    const int g = blockIdx.x, b = blockIdx.y, sp = blockIdx.z;
+    const int lane = threadIdx.x;
+    const int gid = lane >> 2, tig = lane & 3;
+    const int G = Hq / Hkv;
+    // host-staged inputs: independent of the upstream kernel
+    const int L = seq_lens[b];
+    int chunk = (L + num_splits - 1) / num_splits;
+    chunk = (chunk + kMmaTile - 1) / kMmaTile * kMmaTile;
+    const int begin = sp * chunk;
+    const int end = min(L, begin + chunk);
+    const int n_tiles = end > begin ? (end - begin + kMmaTile - 1) / kMmaTile : 0;
+    const int* bt = block_table + static_cast<long long>(b) * max_blocks;
+    // the tile that holds token L-1 (written by this step) may only be read after the wait
+    const int fresh_tile = (end == L && n_tiles > 0) ? n_tiles - 1 : -1;
+
+    auto issue_tile = [&](int t) {
+        const int tok0 = begin + t * kMmaTile;
+        const int page = __ldg(bt + tok0 / block_size);
+        const long long base = ((static_cast<long long>(page) * Hkv + g) * block_size + tok0 % block_size) * D;
+        uint8_t* sk = smem + (t % kClStages) * 2 * TILE_BYTES;
+        uint8_t* sv = sk + TILE_BYTES;
+#pragma unroll
+        for (int i = lane; i < kMmaTile * CH; i += 32) {
+            const int r = i / CH, c = i % CH;
+            const uint32_t so = static_cast<uint32_t>(r * (D * 2) + ((c ^ (r & 7)) << 4));
+            const bool valid = tok0 + r < end;
+            dec_cp_async16(sk + so, k_cache + base + r * D + c * 8, valid);
+            dec_cp_async16(sv + so, v_cache + base + r * D + c * 8, valid);
+        }
+    };
+    // prologue: commit groups stay in tile order. Old tiles go out before the wait; the fresh tile (always
+    // the last tile of the sequence) and the empty groups that pad the ring follow after it.
+    int t_pre = 0;
+    for (; t_pre < kClStages - 1; ++t_pre) {
+        if (t_pre >= n_tiles || t_pre == fresh_tile) break;
+        issue_tile(t_pre);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    pdl_wait();
+    for (int t = t_pre; t < kClStages - 1; ++t) {
+        if (t < n_tiles) issue_tile(t);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+
+    uint32_t qa[D / 16][2];
+    {
+        const uint32_t* qrow =
+            reinterpret_cast<const uint32_t*>(q + (static_cast<long long>(b) * Hq + g * G + min(gid, G - 1)) * D);
+#pragma unroll
+        for (int kk = 0; kk < D / 16; ++kk) {
+            qa[kk][0] = gid < G ? __ldg(qrow + kk * 8 + tig) : 0u;
+            qa[kk][1] = gid < G ? __ldg(qrow + kk * 8 + 4 + tig) : 0u;
+        }
+    }
+    float o_acc[D / 8][4];
+#pragma unroll
+    for (int i = 0; i < D / 8; ++i) o_acc[i][0] = o_acc[i][1] = o_acc[i][2] = o_acc[i][3] = 0.f;
+    float m_run = -INFINITY, l_run = 0.f;
+
+    for (int t = 0; t < n_tiles; ++t) {
+        if (t + kClStages - 1 < n_tiles) issue_tile(t + kClStages - 1);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        asm volatile("cp.async.wait_group %0;" ::"n"(kClStages - 1) : "memory");
+        __syncwarp();
+        const uint8_t* sk = smem + (t % kClStages) * 2 * TILE_BYTES;
+        const uint8_t* sv = sk + TILE_BYTES;
+        float sc[2][4];
+#pragma unroll
+        for (int nb = 0; nb < 2; ++nb) sc[nb][0] = sc[nb][1] = sc[nb][2] = sc[nb][3] = 0.f;
+#pragma unroll
+        for (int kk = 0; kk < D / 16; ++kk) {
+            uint32_t b0, b1, b2, b3;
+            const int r = (lane & 7) + (lane >> 4) * 8;
+            const int c = kk * 2 + ((lane >> 3) & 1);
+            dec_ldsm_x4(smem_u32(sk + r * (D * 2) + ((c ^ (r & 7)) << 4)), b0, b1, b2, b3);
+            dec_mma(sc[0], qa[kk][0], 0u, qa[kk][1], 0u, b0, b1);
+            dec_mma(sc[1], qa[kk][0], 0u, qa[kk][1], 0u, b2, b3);
+        }
+        const int tok0 = begin + t * kMmaTile;
+        float mx = -INFINITY;
+#pragma unroll
+        for (int nb = 0; nb < 2; ++nb) {
+            const int col = tok0 + nb * 8 + 2 * tig;
+            if (col >= end) sc[nb][0] = -INFINITY;
+            if (col + 1 >= end) sc[nb][1] = -INFINITY;
+            mx = fmaxf(mx, fmaxf(sc[nb][0], sc[nb][1]));
+        }
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+        const float mn = fmaxf(m_run, mx);
+        const float mref = mn * scale_log2;
+        const float corr = exp2f(m_run * scale_log2 - mref);
+        m_run = mn;
+        const float p00 = exp2f(sc[0][0] * scale_log2 - mref), p01 = exp2f(sc[0][1] * scale_log2 - mref);
+        const float p10 = exp2f(sc[1][0] * scale_log2 - mref), p11 = exp2f(sc[1][1] * scale_log2 - mref);
+        l_run = l_run * corr + (p00 + p01) + (p10 + p11);
+        const uint32_t pa0 = pack_bf16(p00, p01), pa2 = pack_bf16(p10, p11);
+#pragma unroll
+        for (int db = 0; db < D / 8; ++db) {
+            o_acc[db][0] *= corr;
+            o_acc[db][1] *= corr;
+        }
+#pragma unroll
+        for (int db2 = 0; db2 < D / 16; ++db2) {
+            uint32_t b0, b1, b2, b3;
+            const int r = (lane & 7) + ((lane >> 3) & 1) * 8;
+            const int c = db2 * 2 + (lane >> 4);
+            dec_ldsm_x4_t(smem_u32(sv + r * (D * 2) + ((c ^ (r & 7)) << 4)), b0, b1, b2, b3);
+            dec_mma(o_acc[2 * db2], pa0, 0u, pa2, 0u, b0, b1);
+            dec_mma(o_acc[2 * db2 + 1], pa0, 0u, pa2, 0u, b2, b3);
+        }
+        __syncwarp();
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+
+    // ---- park this split's (o, m, l) in shared memory, then merge across the cluster through DSMEM
+    l_run += __shfl_xor_sync(0xffffffffu, l_run, 1);
+    l_run += __shfl_xor_sync(0xffffffffu, l_run, 2);
+    if (gid < G) {
+#pragma unroll
+        for (int db = 0; db < D / 8; ++db) {
+            red[gid * D + db * 8 + 2 * tig] = o_acc[db][0];
+            red[gid * D + db * 8 + 2 * tig + 1] = o_acc[db][1];
+        }
+        if (tig == 0) {
+            red[G * D + gid] = m_run == -INFINITY ? -INFINITY : m_run * scale_log2;
+            red[G * D + G + gid] = l_run;
+        }
+    }
+    __syncwarp();
+    cluster_sync_all();
+    const int S = num_splits;
+    const int E = G * D;                       // output elements of this (sequence, KV head)
+    const int per = (E + S - 1) / S;           // slice of CTA `sp`
+    for (int e = sp * per + lane; e < min(E, (sp + 1) * per); e += 32) {
+        const int j = e / D;
+        float M = -INFINITY;
+        for (int s2 = 0; s2 < S; ++s2) M = fmaxf(M, dsmem_ld_f32(&red[G * D + j], s2));
+        float o = 0.f, ls = 0.f;
+        for (int s2 = 0; s2 < S; ++s2) {
+            const float f = safe_exp2_diff(dsmem_ld_f32(&red[G * D + j], s2), M);
+            o += dsmem_ld_f32(&red[e], s2) * f;
+            ls += dsmem_ld_f32(&red[G * D + G + j], s2) * f;
+        }
+        const long long h = static_cast<long long>(b) * Hq + g * G + j;
+        out[h * D + (e - j * D)] = __float2bfloat16_rn(ls > 0.f ? o / ls : 0.f);
+    }
+    __syncwarp();
+    cluster_sync_all();  // nobody leaves while a peer may still be reading its shared memory
+}
+
 // out[h, :] = sum_s o_s * 2^(m_s - M) / sum_s l_s * 2^(m_s - M)
 __global__ void attn_decode_reduce_kernel(const float* __restrict__ ws_o, const float* __restrict__ ws_ml,
                                           __nv_bfloat16* __restrict__ out, int D, int num_splits) {
@@ -422,6 +625,19 @@ __global__ void attn_decode_reduce_kernel(const float* __restrict__ ws_o, const 
     }
 }
 
+// The cluster variant is opt-in (ATX_DECODE_CLUSTER=1). Measured on B200 (r01): faster in isolation
+// (14.8 vs 18.9 us at 6 x 1152 tokens) but slower inside the decode graph (3.07 vs 2.91 ms per step):
+// 16-CTA clusters have to be co-scheduled on one GPC while PDL-launched GEMM CTAs hold the shared memory.
+static const bool g_decode_cluster = [] {
+    const char* e = getenv("ATX_DECODE_CLUSTER");
+    return e && e[0] == '1';
+}();
+
+static const bool g_decode_early_prefetch = [] {
+    const char* e = getenv("ATX_DECODE_PREFETCH");
+    return !(e && e[0] == '0');
+}();
+
 template <int D, int G>
 static int launch_decode(const void* q, const void* kc, const void* vc, const int* bt, const int* sl, void* out,
                          float* ws_o, float* ws_ml, int B, int Hq, int Hkv, int block_size, int max_blocks,
@@ -434,6 +650,30 @@ static int launch_decode(const void* q, const void* kc, const void* vc, const in
     cfg.numAttrs = (flags & ATX_FLAG_PDL) ? 1 : 0;
     cfg.gridDim = dim3(static_cast<unsigned>(Hkv), static_cast<unsigned>(B), static_cast<unsigned>(num_splits));
     cfg.stream = stream;
+    if (block_size % kMmaTile == 0 && G <= 8 && num_splits > 1 && num_splits <= 16 && g_decode_cluster) {
+        static bool attr_done[64] = {false};
+        int dev = 0;
+        ATX_CUDA(cudaGetDevice(&dev));
+        if (dev >= 0 && dev < 64 && !attr_done[dev]) {
+            ATX_CUDA(cudaFuncSetAttribute(attn_decode_cluster_kernel<D>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+            attr_done[dev] = true;
+        }
+        cudaLaunchAttribute cattr[2];
+        cattr[0].id = cudaLaunchAttributeClusterDimension;
+        cattr[0].val.clusterDim.x = 1;
+        cattr[0].val.clusterDim.y = 1;
+        cattr[0].val.clusterDim.z = static_cast<unsigned>(num_splits);
+        cattr[1] = attr[0];
+        cfg.attrs = cattr;
+        cfg.numAttrs = (flags & ATX_FLAG_PDL) ? 2 : 1;
+        cfg.blockDim = dim3(32);
+        ATX_CUDA(cudaLaunchKernelEx(&cfg, attn_decode_cluster_kernel<D>, reinterpret_cast<const __nv_bfloat16*>(q),
+                                    reinterpret_cast<const __nv_bfloat16*>(kc),
+                                    reinterpret_cast<const __nv_bfloat16*>(vc), bt, sl,
+                                    reinterpret_cast<__nv_bfloat16*>(out), Hq, Hkv, block_size, max_blocks, num_splits,
+                                    scale * 1.4426950408889634f, g_decode_early_prefetch ? 1 : 0));
+        return ATX_OK;
+    }
     if (block_size % kMmaTile == 0 && G <= 8) {
         cfg.blockDim = dim3(32);
         ATX_CUDA(cudaLaunchKernelEx(&cfg, attn_decode_mma_kernel<D>, reinterpret_cast<const __nv_bfloat16*>(q),

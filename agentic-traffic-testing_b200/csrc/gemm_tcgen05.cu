@@ -299,6 +299,7 @@ struct atx_gemm_plan {
 using namespace atx;
 
 // k-blocks (16 KB each) of weights a CTA prefetches into L2 before it waits for the upstream grid
+static thread_local int tl_l2_prefetch_kb = 0;
 static int g_l2_prefetch_kb = 0;  // measured on B200: prefetching ahead of the TMA ring costs bandwidth (r01)
 
 template <int TN>
@@ -329,7 +330,7 @@ static int launch_gemm(const atx_gemm_plan* p, int ti, void* out, long long ldo,
     cfg.numAttrs = pdl ? 1 : 0;
     ATX_CUDA(cudaLaunchKernelEx(&cfg, gemm_wt_kernel<TN>, p->tmW, p->tmX[ti], out, ldo, T,
                                 static_cast<int>(p->N), kb_total, kb_per, mode, p->w_evict_first,
-                                pdl ? g_l2_prefetch_kb : 0));
+                                pdl ? tl_l2_prefetch_kb : 0));
     return ATX_OK;
 }
 
@@ -392,6 +393,8 @@ int atx_gemm_run(const atx_gemm_plan* p, void* out, long long ldo, int T, int mo
     ATX_REQUIRE(splits == 1 || mode == ATX_GEMM_ADD_F32,
                 "atx_gemm_run: split-K (%d) needs ATX_GEMM_ADD_F32 into a zeroed or residual buffer", splits);
     const int pdl = (flags & ATX_FLAG_PDL) ? 1 : 0;
+    // per-call L2 prefetch depth (k-blocks) in bits 8..15 of flags overrides the process-wide default
+    tl_l2_prefetch_kb = ((flags >> 8) & 0xff) ? ((flags >> 8) & 0xff) : g_l2_prefetch_kb;
     if (T <= 16) return launch_gemm<16>(p, 0, out, ldo, T, mode, splits, pdl, stream);
     if (T <= 32) return launch_gemm<32>(p, 1, out, ldo, T, mode, splits, pdl, stream);
     if (T <= 64) return launch_gemm<64>(p, 2, out, ldo, T, mode, splits, pdl, stream);

@@ -32,6 +32,9 @@ typedef void* atx_stream_t; /* a cudaStream_t */
 
 /* flags */
 #define ATX_FLAG_PDL 1 /* launch with programmatic dependent launch (stream serialization) */
+/* atx_gemm_run only: prefetch this many 16 KB weight slices per CTA into L2 before waiting for the
+ * upstream kernel (useful for a GEMM that sits behind a long non-GEMM chain, e.g. o_proj behind attention) */
+#define ATX_FLAG_L2_PREFETCH(kb) (((kb) & 0xff) << 8)
 
 /* Thread-local text of the last error raised on the calling thread. Never NULL. */
 const char* atx_last_error(void);
