@@ -34,7 +34,10 @@ struct GemmCfg {
     static constexpr int kStageBytesX = TN * kBK * 2;
     static constexpr int kStageBytes = kStageBytesW + kStageBytesX;
     // decode tiles stay small enough for several CTAs per SM; prefill tiles take most of the SM
-    static constexpr int kStages = TN <= 32 ? 5 : (TN <= 64 ? 6 : (TN <= 128 ? 6 : 4));
+#ifndef ATX_STAGES_SMALL
+#define ATX_STAGES_SMALL 6
+#endif
+    static constexpr int kStages = TN <= 32 ? ATX_STAGES_SMALL : (TN <= 64 ? 6 : (TN <= 128 ? 6 : 4));
     static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
     static constexpr uint32_t kTmemCols = TN < 32 ? 32 : TN;
 };
