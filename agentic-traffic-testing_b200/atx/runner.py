@@ -80,6 +80,9 @@ class ModelRunner:
         self.act = torch.zeros(T, I, dtype=bf, device=dev)
         self.part = torch.zeros(T, H, dtype=f32, device=dev) if tp > 1 else None  # partial o/down sums (TP)
         self.allreduce_calls = 0
+        self.fused_ar = False
+        if tp > 1 and os.environ.get("ATX_TP_ALLREDUCE", "fused") == "fused":
+            self._setup_fused_allreduce(T, H)
         self.xl = torch.zeros(S, H, dtype=bf, device=dev)
         self.logits = torch.zeros(S, V, dtype=f32, device=dev)
         self.out_ids = torch.zeros(S, dtype=i32, device=dev)
@@ -153,9 +156,6 @@ class ModelRunner:
         self._h2d_done = torch.cuda.Event()
         self.flags = _cabi.FLAG_PDL if e.use_pdl else 0
         self.lib.atx_gemm_set_l2_prefetch(int(os.environ.get("ATX_L2_PREFETCH_KB", "0")))
-        # o_proj waits behind rope + attention: let its CTAs pull their weight slices into L2 meanwhile
-        self._ablate = set(filter(None, os.environ.get("ATX_ABLATE", "").split(",")))
-        self.o_prefetch = (int(os.environ.get("ATX_O_PREFETCH_KB", "0")) & 0xff) << 8
         self.scale = float(m.head_dim) ** -0.5
         self.launches_last_step = 0
         self.kernel_launches = 0  # cumulative count of our kernels launched (graph replays included)
@@ -173,10 +173,12 @@ class ModelRunner:
         """Issue every kernel of one step on the current stream. Returns the launch count.
 
         Tensor parallel (tp > 1, Megatron split: q/k/v/gate/up by output features = heads, o/down by
-        input features): o_proj and down_proj produce PARTIAL sums into `part`; NCCL all-reduces it
-        over NVLink and the next RMSNorm folds it into the residual stream (`h += part`, part cleared).
-        The LM head is vocabulary-parallel: each rank fills its column slice of a zeroed logits buffer
-        and one all-reduce assembles the full rows, so every rank samples the same token."""
+        input features): o_proj and down_proj produce PARTIAL sums. For decode-sized steps the
+        all-reduce, the residual add and the following RMSNorm are one kernel over NVLink peer memory
+        (atx_allreduce_add_rmsnorm, ping-pong symmetric buffers); prefill-sized steps use NCCL's ring and
+        fold the reduced partial into the residual inside the RMSNorm kernel (`add`). The LM head is
+        vocabulary-parallel: each rank fills its column slice of a zeroed logits buffer and one NCCL
+        all-reduce assembles the rows, so every rank samples the same token."""
         lib, m, w, ck = self.lib, self.m, self.w, self._ck
         st = torch.cuda.current_stream().cuda_stream
         fl = self.flags
@@ -187,59 +189,74 @@ class ModelRunner:
         q_size, qkv_size = Hq * D, (Hq + 2 * Hkv) * D
         dp = self._dp
         h, xn, qkv, q, attn, act = (t.data_ptr() for t in (self.h, self.xn, self.qkv, self.q, self.attn, self.act))
-        part = self.part.data_ptr() if tp > 1 else None
-        proj_out = part if tp > 1 else h      # where o_proj / down_proj accumulate
+        fused = tp > 1 and self.fused_ar and T <= self.FUSED_AR_MAX_T
+        if tp == 1:
+            targets = (h, h)                      # projections add straight into the residual stream
+        elif fused:
+            targets = (self.sym_part[0].data_ptr(), self.sym_part[1].data_ptr())
+        else:
+            self.part[:T].zero_()
+            targets = (self.part.data_ptr(),) * 2
         n = 0
-        abl = self._ablate  # timing studies only (ATX_ABLATE=attn,rope,norm,reduce): skipped kernels => wrong results
+        k = 0            # index of the next projection whose partial sum needs reducing (TP)
+        pending = None   # None | buffer index (fused) | True (NCCL-reduced partial waiting in self.part)
+
+        def norm(w_ptr: int, out_ptr: int, zero_ptr=None, zero_bytes: int = 0, rows_ptr=None, rows_n: int = T) -> None:
+            nonlocal n
+            if tp > 1 and fused and pending is not None:
+                self._fused_norm(pending, T, w_ptr, out_ptr, rows_ptr, rows_n, zero_ptr, zero_bytes, st)
+            else:
+                add = self.part.data_ptr() if (tp > 1 and pending is not None) else None
+                ck(lib.atx_rmsnorm(h, add, rows_ptr, w_ptr, out_ptr, rows_n, H, m.rms_norm_eps, zero_ptr, zero_bytes, fl,
+                                   st))
+            n += 1
+
+        def project(plan) -> None:
+            """o_proj / down_proj: accumulate into the residual (tp 1) or into this round's partial buffer."""
+            nonlocal n, k, pending
+            ck(lib.atx_gemm_run(plan._h, targets[k % 2], H, T, _cabi.GEMM_ADD_F32, 0, fl, st))
+            n += 1
+            if tp > 1:
+                if fused:
+                    pending = k % 2
+                else:
+                    self._all_reduce(self.part[:T])
+                    pending = True
+                k += 1
+
         ck(lib.atx_embed_gather(dp["ids"], w.embed.data_ptr(), h, T, H, V, st))
         n += 1
-        if tp > 1:
-            self.part[:T].zero_()
         sp_qkv = lib.atx_gemm_auto_splits(qkv_size, H, T)
         qb = q_size * 2  # bytes per row of q / attn
-        pending = None   # partial buffer waiting to be folded into h by the next norm
         for li, l in enumerate(w.layers):
             p_qkv, p_o, p_gu, p_down = self.plans[li]
             kc, vc = self.k_cache[li].data_ptr(), self.v_cache[li].data_ptr()
-            if "norm" in abl:
-                pass
-            elif sp_qkv > 1:
-                ck(lib.atx_rmsnorm(h, pending, None, l.ln1.data_ptr(), xn, T, H, m.rms_norm_eps, qkv, T * qkv_size * 4,
-                                   fl, st))
+            if sp_qkv > 1:   # split-K accumulates into qkv: the norm kernel's spare CTAs clear it
+                norm(l.ln1.data_ptr(), xn, qkv, T * qkv_size * 4)
                 ck(lib.atx_gemm_run(p_qkv._h, qkv, qkv_size, T, _cabi.GEMM_ADD_F32, sp_qkv, fl, st))
             else:
-                ck(lib.atx_rmsnorm(h, pending, None, l.ln1.data_ptr(), xn, T, H, m.rms_norm_eps, None, 0, fl, st))
+                norm(l.ln1.data_ptr(), xn)
                 ck(lib.atx_gemm_run(p_qkv._h, qkv, qkv_size, T, _cabi.GEMM_STORE_F32, 1, fl, st))
-            if "norm" in abl:
-                ck(lib.atx_gemm_run(p_qkv._h, qkv, qkv_size, T, _cabi.GEMM_ADD_F32, sp_qkv, fl, st))
-            if "rope" not in abl:
-              ck(lib.atx_rope_kv_write(qkv, dp["pos"], dp["slots"], self.rope.data_ptr(), q, kc, vc, T, Hq, Hkv, D,
+            ck(lib.atx_rope_kv_write(qkv, dp["pos"], dp["slots"], self.rope.data_ptr(), q, kc, vc, T, Hq, Hkv, D,
                                      self.bs, fl, st))
-            n += 3
-            if n_dec and "attn" not in abl:
+            n += 2
+            if n_dec:
                 ck(lib.atx_paged_attn_decode(q, kc, vc, dp["dec_bt"], dp["dec_lens"], attn, self.ws.data_ptr(),
-                                             self.ws.numel() * 4, n_dec, Hq, Hkv, D, self.bs, self.MB,
-                                             1 if "reduce" in abl else dec_splits, self.scale, fl, st))
+                                             self.ws.numel() * 4, n_dec, Hq, Hkv, D, self.bs, self.MB, dec_splits,
+                                             self.scale, fl, st))
                 n += 2 if dec_splits > 1 else 1
             if n_pf:
                 ck(lib.atx_paged_attn_prefill(q + n_dec * qb, kc, vc, dp["pf_bt"], dp["pf_cu"], dp["pf_ctx"],
                                               attn + n_dec * qb, n_pf, max_q, Hq, Hkv, D, self.bs, self.MB,
                                               self.scale, fl, st))
                 n += 1
-            ck(lib.atx_gemm_run(p_o._h, proj_out, H, T, _cabi.GEMM_ADD_F32, 0, fl | self.o_prefetch, st))
-            if tp > 1:
-                self._all_reduce(self.part[:T])
-                pending = part
-            if "norm" not in abl:
-                ck(lib.atx_rmsnorm(h, pending, None, l.ln2.data_ptr(), xn, T, H, m.rms_norm_eps, None, 0, fl, st))
+            project(p_o)
+            norm(l.ln2.data_ptr(), xn)
             ck(lib.atx_gemm_run(p_gu._h, act, I, T, _cabi.GEMM_SWIGLU_BF16, 1, fl, st))  # silu(g)*u in the epilogue
-            ck(lib.atx_gemm_run(p_down._h, proj_out, H, T, _cabi.GEMM_ADD_F32, 0, fl, st))
-            if tp > 1:
-                self._all_reduce(self.part[:T])
-            n += 4
+            n += 1
+            project(p_down)
         if n_rows:
-            ck(lib.atx_rmsnorm(h, pending, dp["rows"], w.norm.data_ptr(), self.xl.data_ptr(), n_rows, H, m.rms_norm_eps,
-                               None, 0, fl, st))
+            norm(w.norm.data_ptr(), self.xl.data_ptr(), rows_ptr=dp["rows"], rows_n=n_rows)
             if tp > 1:
                 Vl = V // tp
                 self.logits[:n_rows].zero_()
@@ -251,8 +268,53 @@ class ModelRunner:
                                     st))
             ck(lib.atx_sample(self.logits.data_ptr(), V, dp["temps"], dp["top_p"], dp["seeds"], dp["steps"],
                               self.out_ids.data_ptr(), n_rows, V, fl, st))
-            n += 3
+            n += 2
+        elif fused:
+            # nothing samples this step, but the ping-pong invariant (one clean buffer) still has to advance
+            norm(w.norm.data_ptr(), xn)
         return n
+
+    # rows up to which a step uses the fused one-shot all-reduce (beyond: NCCL's bandwidth-optimal ring)
+    FUSED_AR_MAX_T = 256
+
+    def _setup_fused_allreduce(self, T: int, H: int) -> None:
+        """Symmetric (peer-mapped) ping-pong partial buffers + flag arrays for atx_allreduce_add_rmsnorm.
+        torch's symmetric-memory allocator is used only to obtain peer-mapped memory; the kernel is ours."""
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+
+        group = self.tp_group if self.tp_group is not None else dist.group.WORLD
+        rows = min(T, self.FUSED_AR_MAX_T)
+        try:
+            self.sym_part = symm.empty((2, rows, H), dtype=torch.float32, device=self.dev)
+            self.sym_part.zero_()
+            hp = symm.rendezvous(self.sym_part, group)
+            self.sym_flags = symm.empty((64,), dtype=torch.int32, device=self.dev)
+            self.sym_flags.zero_()
+            hf = symm.rendezvous(self.sym_flags, group)
+        except Exception as exc:  # no peer mapping on this box: keep the NCCL path, loudly
+            print(f"[atx] symmetric memory unavailable ({exc!r}); tensor-parallel all-reduce stays on NCCL", flush=True)
+            return
+        stride = rows * H * 4
+        vp = C.c_void_p
+        self._ar_parts = [(vp * self.tp)(*[int(p) + b * stride for p in hp.buffer_ptrs]) for b in (0, 1)]
+        self._ar_flags = (vp * self.tp)(*[int(p) for p in hf.buffer_ptrs])
+        self._ar_state = torch.zeros(2, dtype=torch.int32, device=self.dev)
+        self._ar_handles = (hp, hf)
+        torch.cuda.synchronize(self.dev)
+        dist.barrier(group=group)
+        self.fused_ar = True
+
+    def _fused_norm(self, buf: int, T: int, w_ptr: int, out_ptr: int, rows_ptr, n_rows: int, zero_ptr, zero_bytes: int,
+                    st: int) -> None:
+        """all-reduce(part[buf]) + residual add + RMSNorm; hands the other buffer back zeroed."""
+        m = self.m
+        other = self.sym_part[1 - buf].data_ptr()
+        self._ck(self.lib.atx_allreduce_add_rmsnorm(
+            self.h.data_ptr(), self._ar_parts[buf], self._ar_flags, other, T, self._ar_state.data_ptr(), self.tp_rank,
+            self.tp, rows_ptr, w_ptr, out_ptr, n_rows, m.hidden_size, m.rms_norm_eps, zero_ptr, zero_bytes, self.flags,
+            st))
+        self.allreduce_calls += 1
 
     def _all_reduce(self, t: torch.Tensor) -> None:
         import torch.distributed as dist

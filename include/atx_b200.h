@@ -80,6 +80,21 @@ int atx_embed_gather(const int* ids, const void* table, float* out, int T, int H
 int atx_rmsnorm(float* x, float* add, const int* rows, const void* w, void* out, int T, int H, float eps,
                 void* zero_ptr, long long zero_bytes, int flags, atx_stream_t stream);
 
+/* ---- tensor-parallel: all-reduce + residual add + RMSNorm in one kernel over NVLink peer memory -----
+ * Replaces the NCCL all-reduce vLLM issues after o_proj / down_proj of a tensor-parallel Llama layer
+ * (the reference reaches it through llm/serve_llm.py:374-379) together with the residual add and
+ * LlamaRMSNorm that follow (modeling_llama.py:313-332, 62-67). One process per GPU; every rank calls
+ * it with the same T.  part_ptrs[p] / flag_ptrs[p] (HOST arrays of `world` device pointers) are rank
+ * p's partial-sum buffer [T, H] fp32 and flag array int[world], both mapped into this process
+ * (symmetric / IPC memory).  x += sum_p part_p (written back unless `rows` gathers), out = bf16 norm.
+ * clear_buf (nullable): the OTHER ping-pong partial buffer of this rank, first clear_rows rows are
+ * zeroed after the cross-GPU barrier.  state: int[2] in local device memory, zero-initialised once.
+ * zero_ptr / zero_bytes as in atx_rmsnorm. */
+int atx_allreduce_add_rmsnorm(float* x, const void* const* part_ptrs, void* const* flag_ptrs, void* clear_buf,
+                              int clear_rows, int* state, int rank, int world, const int* rows, const void* w,
+                              void* out, int T, int H, float eps, void* zero_ptr, long long zero_bytes, int flags,
+                              atx_stream_t stream);
+
 /* ---- RoPE + KV-cache write ------------------------------------------------------------------------
  * Replaces apply_rotary_pos_emb (modeling_llama.py:146-168, rotate_half layout :138-143) and
  * past_key_values.update (:267) / vLLM reshape_and_cache. qkv: [T, (Hq + 2*Hkv) * D] fp32 (GEMM

@@ -13,7 +13,7 @@ pytestmark = pytest.mark.gpu
 GOLD = Path(__file__).parent / "golden"
 
 
-def _rank(rank, world, port, graphs, q):
+def _rank(rank, world, port, graphs, mode, q):
     import sys
 
     root = Path(__file__).resolve().parent.parent
@@ -27,6 +27,7 @@ def _rank(rank, world, port, graphs, q):
     from oracle import llama_ref as R
 
     os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    os.environ["ATX_TP_ALLREDUCE"] = mode
     torch.cuda.set_device(rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     try:
@@ -42,14 +43,18 @@ def _rank(rank, world, port, graphs, q):
         first = eng.runner.logits[0].float().cpu().numpy()
         while eng.has_work():
             eng.step()
-        q.put((rank, float(np.abs(first - g["logits_last"]).max()), seq.output_ids, eng.runner.allreduce_calls))
+        q.put((rank, float(np.abs(first - g["logits_last"]).max()), seq.output_ids, eng.runner.allreduce_calls,
+               eng.runner.fused_ar))
         eng.runner.close()
     finally:
         dist.destroy_process_group()
 
 
+@pytest.mark.parametrize("mode", ["fused", "nccl"])
 @pytest.mark.parametrize("graphs", [False, True])
-def test_tp2_matches_hf_golden(graphs):
+def test_tp2_matches_hf_golden(graphs, mode):
+    """mode 'fused': all-reduce + residual add + RMSNorm in one kernel over NVLink peer memory
+    (atx_allreduce_add_rmsnorm); mode 'nccl': NCCL all-reduce + fused add/norm kernel."""
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     with socket.socket() as s:
@@ -57,7 +62,7 @@ def test_tp2_matches_hf_golden(graphs):
         port = s.getsockname()[1]
     ctx = tmp.get_context("spawn")
     q = ctx.Queue()
-    procs = [ctx.Process(target=_rank, args=(r, 2, port, graphs, q)) for r in range(2)]
+    procs = [ctx.Process(target=_rank, args=(r, 2, port, graphs, mode, q)) for r in range(2)]
     for p in procs:
         p.start()
     try:
@@ -70,8 +75,10 @@ def test_tp2_matches_hf_golden(graphs):
             if p.is_alive():
                 p.kill()
     gold = np.load(GOLD / "hf_tiny.npz")["greedy"][:16].tolist()
-    (r0, e0, ids0, ar0), (r1, e1, ids1, ar1) = got
-    print(f"\n[tp2 graphs={graphs}] logits max-abs vs HF fp32: rank0 {e0:.4f} rank1 {e1:.4f}; all-reduces {ar0}")
+    (r0, e0, ids0, ar0, f0), (r1, e1, ids1, ar1, f1) = got
+    print(f"\n[tp2 graphs={graphs} {mode}] logits max-abs vs HF fp32: rank0 {e0:.4f} rank1 {e1:.4f}; all-reduces {ar0}; "
+          f"fused kernel active: {f0}")
+    assert f0 == f1 == (mode == "fused")
     assert ids0 == ids1 == gold           # both ranks sample the same tokens, equal to HF greedy
     assert e0 <= 2e-2 and e1 <= 2e-2      # literal north-star bound on this fixture
     assert ar0 > 0
