@@ -16,6 +16,7 @@
 // for o_proj / down_proj IS the fp32 residual stream (residual add fused, no workspace).
 #include "common.cuh"
 
+#include <cstdlib>
 #include <mutex>
 #include <new>
 
@@ -37,7 +38,8 @@ struct GemmCfg {
 #ifndef ATX_STAGES_SMALL
 #define ATX_STAGES_SMALL 6
 #endif
-    static constexpr int kStages = TN <= 32 ? ATX_STAGES_SMALL : (TN <= 64 ? 6 : (TN <= 128 ? 6 : 4));
+    // TN=16: 6 x 18 KB and TN=32: 5 x 20 KB both leave room for two CTAs per SM
+    static constexpr int kStages = TN <= 16 ? ATX_STAGES_SMALL : (TN <= 32 ? 5 : (TN <= 64 ? 6 : (TN <= 128 ? 6 : 4)));
     static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
     static constexpr uint32_t kTmemCols = TN < 32 ? 32 : TN;
 };
@@ -46,13 +48,15 @@ template <int TN>
 __global__ void __launch_bounds__(kGemmThreads)
 gemm_wt_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmX,
                void* __restrict__ out, long long ldo, int T, int N, int kb_total, int kb_per_split,
-               int mode, int w_evict_first, int l2_prefetch_kb) {
+               int mode, int w_evict_first, int l2_prefetch_kb, int stages) {
+    // `stages` (<= Cfg::kStages) is the ring depth actually used: CTAs with few k-blocks get a smaller
+    // shared-memory footprint, so more of them are resident per SM
     using Cfg = GemmCfg<TN>;
     extern __shared__ uint8_t smem_raw[];
     // SWIZZLE_128B tiles must sit on 1024-byte boundaries
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                                ~static_cast<uintptr_t>(1023));
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + stages * Cfg::kStageBytes);
     uint64_t* empty_bar = full_bar + Cfg::kStages;
     uint64_t* accum_bar = empty_bar + Cfg::kStages;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_bar + 1);
@@ -70,6 +74,7 @@ gemm_wt_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
         tma_prefetch_desc(&tmX);
 #pragma unroll
         for (int s = 0; s < Cfg::kStages; ++s) {
+            if (s >= stages) break;
             mbar_init(&full_bar[s], 1);
             mbar_init(&empty_bar[s], 1);
         }
@@ -92,7 +97,7 @@ gemm_wt_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
                 // programmatic dependent launch the first weight stages are already in flight
                 // while the producer of X is still finishing; only X waits for it.
                 const uint64_t polW = w_evict_first ? kEvictFirst : kEvictNormal;
-                const int pre = min(nkb, Cfg::kStages);
+                const int pre = min(nkb, stages);
                 for (int i = 0; i < pre; ++i) {
                     mbar_expect_tx(&full_bar[i], Cfg::kStageBytes);
                     tma_load_2d(smem + i * Cfg::kStageBytes, &tmW, &full_bar[i],
@@ -115,7 +120,7 @@ gemm_wt_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
                     tma_load_2d(st, &tmW, &full_bar[stage], (kb_begin + i) * kBK, n0, polW);
                     tma_load_2d(st + Cfg::kStageBytesW, &tmX, &full_bar[stage], (kb_begin + i) * kBK,
                                 t0, kEvictLast);
-                    if (++stage == Cfg::kStages) {
+                    if (++stage == stages) {
                         stage = 0;
                         phase ^= 1;
                     }
@@ -142,7 +147,7 @@ gemm_wt_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
                                   (i > 0 || k > 0) ? 1u : 0u);
                     }
                     umma_commit(&empty_bar[stage]);  // frees the smem slot when the MMAs retire
-                    if (++stage == Cfg::kStages) {
+                    if (++stage == stages) {
                         stage = 0;
                         phase ^= 1;
                     }
@@ -245,6 +250,231 @@ gemm_wt_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
     if (warp == 1) tmem_dealloc<Cfg::kTmemCols>(tmem_acc);
 }
 
+// ---- persistent, warp-specialised variant for prefill-sized token tiles ----------------------------
+// One CTA per SM loops over output tiles; a TMA producer warp, a single-thread MMA issuer and four
+// epilogue warps run as three decoupled pipelines: the smem ring (full/empty mbarriers) between TMA and
+// MMA, and TWO TMEM accumulators (tmem_full/tmem_empty) between MMA and epilogue, so the epilogue of
+// tile i (TMEM -> registers -> global) overlaps the main loop of tile i+1 instead of idling the tensor
+// pipe. Tiles are ordered token-tile-fastest so that CTAs running concurrently share weight tiles in L2.
+constexpr int kPersistThreads = 192;
+constexpr int kXchgBytes = 16 * 1024;  // SwiGLU half-tile exchange, 32 token columns at a time
+
+template <int TN>
+struct PersistCfg {
+    static constexpr int kStageBytesW = kBM * kBK * 2;
+    static constexpr int kStageBytesX = TN * kBK * 2;
+    static constexpr int kStageBytes = kStageBytesW + kStageBytesX;
+    static constexpr int kStages = TN <= 128 ? 6 : 4;
+    static constexpr int kSmemBytes = kStages * kStageBytes + kXchgBytes + 1024 + 256;
+    static constexpr uint32_t kTmemCols = 2 * TN;  // two accumulators
+};
+
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+
+template <int TN>
+__global__ void __launch_bounds__(kPersistThreads, 1)
+gemm_wt_persistent_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmX,
+                          void* __restrict__ out, long long ldo, int T, int N, int kb_total, int tiles_t,
+                          int total_tiles, int mode, int w_evict_first) {
+    using Cfg = PersistCfg<TN>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                               ~static_cast<uintptr_t>(1023));
+    float* xchg = reinterpret_cast<float*>(smem + Cfg::kStages * Cfg::kStageBytes);
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes + kXchgBytes);
+    uint64_t* empty_bar = full_bar + Cfg::kStages;
+    uint64_t* tmem_full = empty_bar + Cfg::kStages;   // [2]
+    uint64_t* tmem_empty = tmem_full + 2;             // [2]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    if (warp == 0 && elect_one()) {
+        tma_prefetch_desc(&tmW);
+        tma_prefetch_desc(&tmX);
+#pragma unroll
+        for (int s = 0; s < Cfg::kStages; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        mbar_init(&tmem_full[0], 1);
+        mbar_init(&tmem_full[1], 1);
+        mbar_init(&tmem_empty[0], 4);  // one arrival per epilogue warp
+        mbar_init(&tmem_empty[1], 4);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    pdl_launch_dependents();
+
+    if (warp == 0) {
+        if (elect_one()) {
+            // ===== TMA producer
+            const uint64_t polW = w_evict_first ? kEvictFirst : kEvictNormal;
+            int stage = 0;
+            uint32_t phase = 0;
+            bool waited = false;
+            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+                const int n0 = (tile / tiles_t) * kBM, t0 = (tile % tiles_t) * TN;
+                for (int kb = 0; kb < kb_total; ++kb) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1);
+                    uint8_t* st = smem + stage * Cfg::kStageBytes;
+                    mbar_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+                    tma_load_2d(st, &tmW, &full_bar[stage], kb * kBK, n0, polW);
+                    if (!waited) {  // weights never depend on the upstream kernel, activations do
+                        pdl_wait();
+                        waited = true;
+                    }
+                    tma_load_2d(st + Cfg::kStageBytesW, &tmX, &full_bar[stage], kb * kBK, t0, kEvictLast);
+                    if (++stage == Cfg::kStages) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (elect_one()) {
+            // ===== MMA issuer
+            constexpr uint32_t idesc = umma_idesc_bf16(kBM, TN);
+            int stage = 0, acc = 0;
+            uint32_t phase = 0, acc_phase = 0;
+            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+                mbar_wait(&tmem_empty[acc], acc_phase ^ 1);  // epilogue has drained this accumulator
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + acc * TN;
+                for (int kb = 0; kb < kb_total; ++kb) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tc_fence_after();
+                    const uint32_t a_addr = smem_u32(smem + stage * Cfg::kStageBytes);
+                    const uint64_t a_desc = umma_desc_sw128(a_addr);
+                    const uint64_t b_desc = umma_desc_sw128(a_addr + Cfg::kStageBytesW);
+#pragma unroll
+                    for (int k = 0; k < kBK / kUK; ++k)
+                        umma_bf16(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+                    umma_commit(&empty_bar[stage]);
+                    if (++stage == Cfg::kStages) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
+                }
+                umma_commit(&tmem_full[acc]);
+                if (++acc == 2) {
+                    acc = 0;
+                    acc_phase ^= 1;
+                }
+            }
+        }
+    } else {
+        // ===== epilogue warps 2..5: TMEM lane quarter = warp % 4
+        const int quarter = warp & 3;
+        const bool gate_warp = quarter < 2;            // SwiGLU: lanes 0-63 gate rows, 64-127 up rows
+        const int feat = (quarter & 1) * 32 + lane;    // feature within the 64-group (SwiGLU)
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        bool waited = false;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+            const int n0 = (tile / tiles_t) * kBM, t0 = (tile % tiles_t) * TN;
+            mbar_wait(&tmem_full[acc], acc_phase);
+            tc_fence_after();
+            if (!waited) {  // `out` may be the residual stream written by the upstream grid
+                pdl_wait();
+                waited = true;
+            }
+            const uint32_t tlane = tmem_base + acc * TN + (static_cast<uint32_t>(quarter * 32) << 16);
+            if (mode == ATX_GEMM_SWIGLU_BF16) {
+                // symmetric exchange in groups of 32 token columns: gate warps finish columns [0, TN/2),
+                // up warps columns [TN/2, TN); each parks the half the other pair needs
+                constexpr int HALF = TN / 2;
+                const long long col = static_cast<long long>(tile / tiles_t) * 64 + feat;
+                const bool ok = col < N / 2;
+                __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out);
+                float* park_mine = xchg + (gate_warp ? 0 : 32 * 64);    // [32][64] floats each
+                float* park_other = xchg + (gate_warp ? 32 * 64 : 0);
+#pragma unroll 1
+                for (int g0 = 0; g0 < HALF; g0 += 32) {
+                    const int c_park = (gate_warp ? HALF : 0) + g0;   // columns whose value the partner needs
+                    const int c_own = (gate_warp ? 0 : HALF) + g0;    // columns this warp finishes
+#pragma unroll
+                    for (int c = 0; c < 32; c += 16) {
+                        uint32_t v[16];
+                        tmem_ld16(tlane + c_park + c, v);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) park_mine[(c + j) * 64 + feat] = __uint_as_float(v[j]);
+                    }
+                    epi_bar_sync();
+#pragma unroll
+                    for (int c = 0; c < 32; c += 16) {
+                        uint32_t v[16];
+                        tmem_ld16(tlane + c_own + c, v);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) {
+                            const int t = t0 + c_own + c + j;
+                            const float mine = __uint_as_float(v[j]), other = park_other[(c + j) * 64 + feat];
+                            const float gg = gate_warp ? mine : other, uu = gate_warp ? other : mine;
+                            if (ok && t < T)
+                                o[static_cast<long long>(t) * ldo + col] =
+                                    __float2bfloat16_rn(gg / (1.f + expf(-gg)) * uu);
+                        }
+                    }
+                    epi_bar_sync();  // the exchange buffer is reused by the next group
+                }
+            } else {
+                const int n = n0 + quarter * 32 + lane;
+                const bool n_ok = n < N;
+#pragma unroll 1
+                for (int c = 0; c < TN; c += 16) {
+                    if (t0 + c >= T) break;
+                    uint32_t v[16];
+                    tmem_ld16(tlane + c, v);
+                    tmem_ld_wait();
+                    if (n_ok) {
+                        if (mode == ATX_GEMM_STORE_F32) {
+                            float* o = reinterpret_cast<float*>(out);
+#pragma unroll
+                            for (int j = 0; j < 16; ++j) {
+                                const int t = t0 + c + j;
+                                if (t < T) o[static_cast<long long>(t) * ldo + n] = __uint_as_float(v[j]);
+                            }
+                        } else if (mode == ATX_GEMM_ADD_F32) {
+                            float* o = reinterpret_cast<float*>(out);
+#pragma unroll
+                            for (int j = 0; j < 16; ++j) {
+                                const int t = t0 + c + j;
+                                if (t < T) atomicAdd(o + static_cast<long long>(t) * ldo + n, __uint_as_float(v[j]));
+                            }
+                        } else {
+                            __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out);
+#pragma unroll
+                            for (int j = 0; j < 16; ++j) {
+                                const int t = t0 + c + j;
+                                if (t < T)
+                                    o[static_cast<long long>(t) * ldo + n] = __float2bfloat16_rn(__uint_as_float(v[j]));
+                            }
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tmem_empty[acc]);  // accumulator free for the tile after next
+            if (++acc == 2) {
+                acc = 0;
+                acc_phase ^= 1;
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+}
+
 // ---- host side ---------------------------------------------------------------------------------------
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -320,11 +550,18 @@ static int launch_gemm(const atx_gemm_plan* p, int ti, void* out, long long ldo,
     const int kb_total = static_cast<int>(p->K / kBK);
     const int kb_per = (kb_total + splits - 1) / splits;
     const int zs = (kb_total + kb_per - 1) / kb_per;
+    int stages = kb_per < Cfg::kStages ? kb_per : Cfg::kStages;
+    // the fused-SwiGLU epilogue parks half a tile in the stage buffers: keep them large enough
+    if (mode == ATX_GEMM_SWIGLU_BF16) {
+        const int need = (TN * 64 * 4 + Cfg::kStageBytes - 1) / Cfg::kStageBytes;
+        if (stages < need) stages = need;
+    }
+    const int smem_bytes = stages * Cfg::kStageBytes + 1024 + 256;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(static_cast<unsigned>((p->N + kBM - 1) / kBM), static_cast<unsigned>((T + TN - 1) / TN),
                        static_cast<unsigned>(zs));
     cfg.blockDim = dim3(kGemmThreads);
-    cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+    cfg.dynamicSmemBytes = smem_bytes;
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
@@ -333,9 +570,46 @@ static int launch_gemm(const atx_gemm_plan* p, int ti, void* out, long long ldo,
     cfg.numAttrs = pdl ? 1 : 0;
     ATX_CUDA(cudaLaunchKernelEx(&cfg, gemm_wt_kernel<TN>, p->tmW, p->tmX[ti], out, ldo, T,
                                 static_cast<int>(p->N), kb_total, kb_per, mode, p->w_evict_first,
-                                pdl ? tl_l2_prefetch_kb : 0));
+                                pdl ? tl_l2_prefetch_kb : 0, stages));
     return ATX_OK;
 }
+
+template <int TN>
+static int launch_gemm_persistent(const atx_gemm_plan* p, int ti, void* out, long long ldo, int T, int mode, int pdl,
+                                  cudaStream_t stream) {
+    using Cfg = PersistCfg<TN>;
+    static bool attr_done[64] = {false};
+    int dev = 0;
+    ATX_CUDA(cudaGetDevice(&dev));
+    if (dev >= 0 && dev < 64 && !attr_done[dev]) {
+        ATX_CUDA(cudaFuncSetAttribute(gemm_wt_persistent_kernel<TN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      Cfg::kSmemBytes));
+        attr_done[dev] = true;
+    }
+    const int kb_total = static_cast<int>(p->K / kBK);
+    const int tiles_n = static_cast<int>((p->N + kBM - 1) / kBM);
+    const int tiles_t = (T + TN - 1) / TN;
+    const int total = tiles_n * tiles_t;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(static_cast<unsigned>(total < num_sms() ? total : num_sms()));
+    cfg.blockDim = dim3(kPersistThreads);
+    cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    ATX_CUDA(cudaLaunchKernelEx(&cfg, gemm_wt_persistent_kernel<TN>, p->tmW, p->tmX[ti], out, ldo, T,
+                                static_cast<int>(p->N), kb_total, tiles_t, total, mode, p->w_evict_first));
+    return ATX_OK;
+}
+
+// ATX_GEMM_PERSISTENT=0 keeps the one-tile-per-CTA kernel for prefill-sized batches too
+static const bool g_gemm_persistent = [] {
+    const char* e = getenv("ATX_GEMM_PERSISTENT");
+    return !(e && e[0] == '0');
+}();
 
 extern "C" {
 
@@ -401,6 +675,10 @@ int atx_gemm_run(const atx_gemm_plan* p, void* out, long long ldo, int T, int mo
     if (T <= 16) return launch_gemm<16>(p, 0, out, ldo, T, mode, splits, pdl, stream);
     if (T <= 32) return launch_gemm<32>(p, 1, out, ldo, T, mode, splits, pdl, stream);
     if (T <= 64) return launch_gemm<64>(p, 2, out, ldo, T, mode, splits, pdl, stream);
+    if (g_gemm_persistent && splits == 1) {
+        if (T <= 128) return launch_gemm_persistent<128>(p, 3, out, ldo, T, mode, pdl, stream);
+        return launch_gemm_persistent<256>(p, 4, out, ldo, T, mode, pdl, stream);
+    }
     if (T <= 128) return launch_gemm<128>(p, 3, out, ldo, T, mode, splits, pdl, stream);
     return launch_gemm<256>(p, 4, out, ldo, T, mode, splits, pdl, stream);
 }
