@@ -75,9 +75,27 @@ def bench_attn():
                           "GBps": round(byts / ms / 1e6, 1)}), flush=True)
 
 
+def bench_prefill_attn():
+    Hq, Hkv, D, bs = 32, 8, 128, 16
+    for S, L in [(6, 1024), (4, 8192), (2, 32768)]:
+        nblk = S * (L // bs)
+        kc = torch.randn(nblk, Hkv, bs, D, device="cuda", dtype=torch.bfloat16)
+        vc = torch.randn_like(kc)
+        bt = torch.arange(nblk, device="cuda", dtype=torch.int32).view(S, -1)
+        q = torch.randn(S * L, Hq * D, device="cuda", dtype=torch.bfloat16)
+        out = torch.empty_like(q)
+        cu = torch.arange(0, (S + 1) * L, L, device="cuda", dtype=torch.int32)
+        ctx = torch.full((S,), L, device="cuda", dtype=torch.int32)
+        ms = time_ms(lambda: _cabi.paged_attn_prefill(q, kc, vc, bt, cu, ctx, out, S, L, Hq, Hkv, D, bs, D ** -0.5),
+                     iters=5, warmup=2)
+        flops = 4.0 * S * Hq * D * (L * (L + 1) / 2)   # causal
+        print(json.dumps({"kernel": "attn_prefill", "S": S, "L": L, "ms": round(ms, 3),
+                          "TFLOPs_causal": round(flops / ms / 1e9, 1)}), flush=True)
+
+
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
-    ap.add_argument("what", choices=["gemm", "attn", "all"])
+    ap.add_argument("what", choices=["gemm", "attn", "prefill", "all"])
     ap.add_argument("--T", type=int, nargs="*", default=[6])
     ap.add_argument("--splits", type=int, nargs="*", default=[0])
     a = ap.parse_args()
@@ -86,3 +104,5 @@ if __name__ == "__main__":
             bench_gemm(T, splits_list=tuple(a.splits))
     if a.what in ("attn", "all"):
         bench_attn()
+    if a.what in ("prefill", "all"):
+        bench_prefill_attn()
