@@ -84,8 +84,8 @@ def load() -> C.CDLL:
     lib.atx_paged_attn_decode_static.argtypes = [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, f32, i32, vp]
     lib.atx_paged_attn_decode_static_capacity.argtypes = []
     lib.atx_paged_attn_decode_static_capacity.restype = i64
-    lib.atx_paged_attn_prefill.argtypes = [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, f32, i32,
-                                           vp]
+    lib.atx_paged_attn_prefill.argtypes = [vp, vp, vp, vp, vp, vp, vp, i32, i32, i64, i64, i32, i32, i32, i32, i32, f32,
+                                           i32, vp]
     lib.atx_sample.argtypes = [vp, i64, vp, vp, vp, vp, vp, i32, i32, i32, vp]
     for name in EXPORTS:  # fail at load time, not at first use, if the build is stale
         getattr(lib, name)
@@ -223,8 +223,9 @@ def paged_attn_prefill(q: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Te
     assert q.dtype == torch.bfloat16 and out.dtype == torch.bfloat16 and block_table.dtype == torch.int32
     assert cu_q.dtype == torch.int32 and ctx_lens.dtype == torch.int32
     _check(load().atx_paged_attn_prefill(q.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(), block_table.data_ptr(),
-                                         cu_q.data_ptr(), ctx_lens.data_ptr(), out.data_ptr(), S, max_q_len, Hq, Hkv,
-                                         D, block_size, block_table.shape[1], scale, flags, _stream()))
+                                         cu_q.data_ptr(), ctx_lens.data_ptr(), out.data_ptr(), S, max_q_len,
+                                         q.shape[0], k_cache.shape[0], Hq, Hkv, D, block_size, block_table.shape[1],
+                                         scale, flags, _stream()))
 
 
 def sample(logits: torch.Tensor, out_ids: torch.Tensor, B: int, V: int, temperature: Optional[torch.Tensor] = None,

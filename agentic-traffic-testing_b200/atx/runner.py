@@ -247,8 +247,8 @@ class ModelRunner:
                 n += 2 if dec_splits > 1 else 1
             if n_pf:
                 ck(lib.atx_paged_attn_prefill(q + n_dec * qb, kc, vc, dp["pf_bt"], dp["pf_cu"], dp["pf_ctx"],
-                                              attn + n_dec * qb, n_pf, max_q, Hq, Hkv, D, self.bs, self.MB,
-                                              self.scale, fl, st))
+                                              attn + n_dec * qb, n_pf, max_q, T - n_dec, self.num_blocks, Hq, Hkv, D,
+                                              self.bs, self.MB, self.scale, fl, st))
                 n += 1
             project(p_o)
             norm(l.ln2.data_ptr(), xn)

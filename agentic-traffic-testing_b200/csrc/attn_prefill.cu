@@ -12,6 +12,8 @@
 // TODO(round 2): move QK^T / PV to tcgen05 with S/P in TMEM for the 32k-token prefill config.
 #include "common.cuh"
 
+#include <cstdlib>
+
 #include "../../include/atx_b200.h"
 
 namespace atx {
@@ -271,15 +273,27 @@ static int launch_prefill(const void* q, const void* kc, const void* vc, const i
     return ATX_OK;
 }
 
+// attn_prefill_tc.cu
+int launch_prefill_tc(const void* q, const void* kc, const void* vc, const int* bt, const int* cu_q, const int* ctx,
+                      void* out, int S, int max_q_len, long long total_q, long long num_blocks, int Hq, int Hkv,
+                      int max_blocks, float scale, int flags, cudaStream_t stream);
+
 }  // namespace atx
 
 using namespace atx;
 
+// ATX_PREFILL_TC=0 keeps the mma.sync kernel for head_dim 128 as well
+static const bool g_prefill_tc = [] {
+    const char* e = getenv("ATX_PREFILL_TC");
+    return !(e && e[0] == '0');
+}();
+
 extern "C" {
 
 int atx_paged_attn_prefill(const void* q, const void* k_cache, const void* v_cache, const int* block_table,
-                           const int* cu_q, const int* ctx_lens, void* out, int S, int max_q_len, int Hq, int Hkv,
-                           int D, int block_size, int max_blocks, float scale, int flags, atx_stream_t stream_) {
+                           const int* cu_q, const int* ctx_lens, void* out, int S, int max_q_len, long long total_q,
+                           long long num_blocks, int Hq, int Hkv, int D, int block_size, int max_blocks, float scale,
+                           int flags, atx_stream_t stream_) {
     cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
     ATX_REQUIRE(q && k_cache && v_cache && block_table && cu_q && ctx_lens && out,
                 "atx_paged_attn_prefill: null pointer");
@@ -287,6 +301,11 @@ int atx_paged_attn_prefill(const void* q, const void* k_cache, const void* v_cac
                     block_size > 0 && max_blocks > 0,
                 "atx_paged_attn_prefill: bad shape S=%d max_q_len=%d Hq=%d Hkv=%d block_size=%d max_blocks=%d", S,
                 max_q_len, Hq, Hkv, block_size, max_blocks);
+    ATX_REQUIRE(total_q >= max_q_len && num_blocks > 0, "atx_paged_attn_prefill: total_q=%lld / num_blocks=%lld", total_q,
+                num_blocks);
+    if (D == 128 && block_size == 16 && g_prefill_tc && (reinterpret_cast<uintptr_t>(q) & 15) == 0)
+        return launch_prefill_tc(q, k_cache, v_cache, block_table, cu_q, ctx_lens, out, S, max_q_len, total_q, num_blocks,
+                                 Hq, Hkv, max_blocks, scale, flags, stream);
     if (D == 128)
         return launch_prefill<128>(q, k_cache, v_cache, block_table, cu_q, ctx_lens, out, S, max_q_len, Hq, Hkv,
                                    block_size, max_blocks, scale, flags, stream);

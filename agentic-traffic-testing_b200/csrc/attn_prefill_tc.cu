@@ -1,0 +1,409 @@
+// Causal prefill attention over the paged KV cache on tcgen05 tensor cores (head_dim 128, 16-token pages).
+//
+// Same arithmetic as attn_prefill.cu (transformers modeling_llama.py:199-222, fp32 softmax :217). The
+// mma.sync version tops out at 42 % of the LEGACY tensor path (232 TFLOP/s, profiles/r01g); here both
+// GEMMs of attention run on tcgen05 with TMEM accumulators:
+//
+//   S  = Q K^T   M=128 query rows, N=128 keys, K=128 dims     A=Q (smem, K-major)  B=K  (smem, K-major)
+//   O += P V     M=128 query rows, N=128 dims, K=128 keys     A=P (smem, K-major)  B=V  (smem, MN-major)
+//
+// One CTA = 128 query rows of one head. Warp 0: TMA producer (Q once; K and V page by page — a page of one
+// KV head is 16 rows x 256 B, loaded as two 128B-swizzled boxes — into 2-deep rings). Warp 1: the single
+// MMA-issuing thread. Warps 2-5: one thread per query row: read S from TMEM, causal mask, online softmax in
+// registers (no shuffles: a thread owns its row), write P as bf16 into the swizzled A-operand layout,
+// rescale O in TMEM only when some row's running max moved, finally normalise and store.
+// S is double-buffered in TMEM so QK^T of tile j+1 overlaps the softmax of tile j.
+#include "common.cuh"
+
+#include <mutex>
+#include <vector>
+
+#include "../../include/atx_b200.h"
+
+namespace atx {
+
+constexpr int kTcBM = 128;   // query rows per CTA
+constexpr int kTcBN = 128;   // keys per tile
+constexpr int kTcD = 128;
+constexpr int kTcThreads = 192;
+constexpr int kTcPage = 16;
+constexpr int kAtomBytes = 128 * 128;            // [128 rows x 64 bf16], 128B-swizzled
+constexpr int kTileBytes = 2 * kAtomBytes;       // [128 x 128] bf16 as two K- (or N-) atoms
+constexpr int kTcSmem = 6 * kTileBytes + 1024 + 256;  // Q, K x2, V x2, P + align + barriers
+
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&v)[16]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+        :
+        : "r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
+          "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
+        : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+// MN-major operand ([K rows][64 contiguous N elements] atoms, 128B swizzle): LBO = distance between the
+// N-atoms, SBO = distance between groups of 8 K-rows (cute::UMMA canonical Major-MN SW128 layout).
+__device__ __forceinline__ uint64_t umma_desc_sw128_mn(uint32_t smem_addr, uint32_t lbo_bytes) {
+    uint64_t d = 0;
+    d |= static_cast<uint64_t>((smem_addr & 0x3FFFFu) >> 4);
+    d |= static_cast<uint64_t>(lbo_bytes >> 4) << 16;
+    d |= static_cast<uint64_t>(1024 >> 4) << 32;
+    d |= static_cast<uint64_t>(1) << 46;
+    d |= static_cast<uint64_t>(2) << 61;
+    return d;
+}
+__device__ __forceinline__ void mbar_arrive_cnt(uint64_t* bar) { mbar_arrive(bar); }
+__device__ __forceinline__ float ex2_approx(float x) {  // one MUFU op; 2^-inf = 0
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+__global__ void __launch_bounds__(kTcThreads, 1)
+attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                       const __grid_constant__ CUtensorMap tmV, const int* __restrict__ block_table,
+                       const int* __restrict__ cu_q, const int* __restrict__ ctx_lens,
+                       __nv_bfloat16* __restrict__ out, int Hq, int Hkv, int max_blocks, float scale_log2) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                               ~static_cast<uintptr_t>(1023));
+    uint8_t* sQ = smem;
+    uint8_t* sK = smem + kTileBytes;          // 2 stages
+    uint8_t* sV = smem + 3 * kTileBytes;      // 2 stages
+    uint8_t* sP = smem + 5 * kTileBytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 6 * kTileBytes);
+    uint64_t* q_full = bars;            // 1
+    uint64_t* k_full = bars + 1;        // 2
+    uint64_t* k_empty = bars + 3;       // 2
+    uint64_t* v_full = bars + 5;        // 2
+    uint64_t* v_empty = bars + 7;       // 2
+    uint64_t* s_full = bars + 9;        // 2
+    uint64_t* p_full = bars + 11;       // 1
+    uint64_t* o_done = bars + 12;       // 1
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 13);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int s = blockIdx.z, h = blockIdx.y;
+    const int q_begin = cu_q[s];
+    const int n_q = cu_q[s + 1] - q_begin;
+    const int m0 = blockIdx.x * kTcBM;
+    if (m0 >= n_q) return;  // whole CTA: before any barrier / TMEM use
+    const int ctx = ctx_lens[s];
+    const int off = ctx - n_q;  // query j sees keys [0, off + j]
+    const int g = h / (Hq / Hkv);
+    const int kv_limit = min(ctx, off + m0 + kTcBM);
+    const int n_tiles = (kv_limit + kTcBN - 1) / kTcBN;
+    const int* bt = block_table + static_cast<long long>(s) * max_blocks;
+
+    if (warp == 0 && elect_one()) {
+        tma_prefetch_desc(&tmQ);
+        tma_prefetch_desc(&tmK);
+        tma_prefetch_desc(&tmV);
+        mbar_init(q_full, 1);
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&k_full[i], 1);
+            mbar_init(&k_empty[i], 1);
+            mbar_init(&v_full[i], 1);
+            mbar_init(&v_empty[i], 1);
+            mbar_init(&s_full[i], 1);
+        }
+        mbar_init(p_full, 128);
+        mbar_init(o_done, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc<512>(tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t tmem_S0 = tmem_base, tmem_O = tmem_base + 256;
+    pdl_launch_dependents();
+
+    if (warp == 0) {
+        // ===== TMA producer: the whole warp works. Lane p owns page p of the tile: the eight block-table
+        // lookups of a tile are one coalesced load (they were a chain of dependent single-thread loads in the
+        // first version, ~5000 cycles per tile), and lane p issues the four boxes (K/V x two 64-dim atoms).
+        pdl_wait();  // q and this chunk's K/V rows come from the upstream kernels
+        if (lane == 0) {
+            mbar_expect_tx(q_full, kTileBytes);
+            tma_load_2d(sQ, &tmQ, q_full, h * kTcD, q_begin + m0, kEvictNormal);
+            tma_load_2d(sQ + kAtomBytes, &tmQ, q_full, h * kTcD + 64, q_begin + m0, kEvictNormal);
+        }
+        auto page_row = [&](int j) -> int {   // first cache row of this lane's page in tile j (or -1)
+            const int kv0 = j * kTcBN;
+            const int pages = min(kTcBN / kTcPage, (ctx - kv0 + kTcPage - 1) / kTcPage);
+            return (j < n_tiles && lane < pages) ? (__ldg(bt + kv0 / kTcPage + lane) * Hkv + g) * kTcPage : -1;
+        };
+        int row_next = page_row(0);
+        for (int j = 0; j < n_tiles; ++j) {
+            const int st = j & 1;
+            const uint32_t ph = (j >> 1) & 1;
+            const int row = row_next;
+            row_next = page_row(j + 1);  // lookup for the next tile is in flight while this one is issued
+            const int pages = min(kTcBN / kTcPage, (ctx - j * kTcBN + kTcPage - 1) / kTcPage);  // allocated pages only
+            if (lane == 0) {
+                mbar_wait(&k_empty[st], ph ^ 1);
+                mbar_expect_tx(&k_full[st], pages * kTcPage * 256);
+            }
+            __syncwarp();
+            if (row >= 0) {
+                uint8_t* dst = sK + st * kTileBytes + lane * kTcPage * 128;
+                tma_load_2d(dst, &tmK, &k_full[st], 0, row, kEvictLast);
+                tma_load_2d(dst + kAtomBytes, &tmK, &k_full[st], 64, row, kEvictLast);
+            }
+            if (lane == 0) {
+                mbar_wait(&v_empty[st], ph ^ 1);
+                mbar_expect_tx(&v_full[st], pages * kTcPage * 256);
+            }
+            __syncwarp();
+            if (row >= 0) {
+                uint8_t* dst = sV + st * kTileBytes + lane * kTcPage * 128;
+                tma_load_2d(dst, &tmV, &v_full[st], 0, row, kEvictLast);
+                tma_load_2d(dst + kAtomBytes, &tmV, &v_full[st], 64, row, kEvictLast);
+            }
+        }
+    } else if (warp == 1) {
+        if (elect_one()) {
+            // ===== MMA issuer
+            constexpr uint32_t idesc_qk = umma_idesc_bf16(kTcBM, kTcBN);                 // A, B K-major
+            constexpr uint32_t idesc_pv = umma_idesc_bf16(kTcBM, kTcD) | (1u << 16);      // B (= V) MN-major
+            auto issue_qk = [&](int j) {
+                const int st = j & 1;
+                mbar_wait(&k_full[st], (j >> 1) & 1);
+                tc_fence_after();
+                const uint32_t qa = smem_u32(sQ), ka = smem_u32(sK + st * kTileBytes);
+#pragma unroll
+                for (int kk = 0; kk < kTcD / 16; ++kk) {
+                    const uint32_t o = (kk >> 2) * kAtomBytes + (kk & 3) * 32;
+                    umma_bf16(tmem_S0 + (j & 1) * kTcBN, umma_desc_sw128(qa + o), umma_desc_sw128(ka + o), idesc_qk,
+                              kk > 0 ? 1u : 0u);
+                }
+                umma_commit(&k_empty[st]);
+                umma_commit(&s_full[j & 1]);
+            };
+            mbar_wait(q_full, 0);
+            issue_qk(0);
+            for (int j = 0; j < n_tiles; ++j) {
+                if (j + 1 < n_tiles) issue_qk(j + 1);  // overlaps the softmax of tile j
+                const int st = j & 1;
+                mbar_wait(&v_full[st], (j >> 1) & 1);
+                mbar_wait(p_full, j & 1);              // P(j) in smem, O rescaled, tail rows of V cleared
+                tc_fence_after();
+                const uint32_t pa = smem_u32(sP), va = smem_u32(sV + st * kTileBytes);
+#pragma unroll
+                for (int kk = 0; kk < kTcBN / 16; ++kk) {
+                    const uint64_t a_desc = umma_desc_sw128(pa + (kk >> 2) * kAtomBytes + (kk & 3) * 32);
+                    const uint64_t b_desc = umma_desc_sw128_mn(va + kk * 16 * 128, kAtomBytes);
+                    umma_bf16(tmem_O, a_desc, b_desc, idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
+                }
+                umma_commit(&v_empty[st]);
+                umma_commit(o_done);
+            }
+        }
+    } else {
+        // ===== softmax / correction / epilogue: thread <-> query row
+        const int quarter = warp & 3;
+        const int row = quarter * 32 + lane;            // row inside the tile == TMEM lane
+        const int qpos = m0 + row;                      // query index inside this sequence's chunk
+        const int limit = off + qpos;                   // last visible key
+        const uint32_t lane_sel = static_cast<uint32_t>(quarter * 32) << 16;
+        float m_run = -INFINITY, l_run = 0.f;
+        for (int j = 0; j < n_tiles; ++j) {
+            const int kv0 = j * kTcBN;
+            mbar_wait(&s_full[j & 1], (j >> 1) & 1);
+            tc_fence_after();
+            const uint32_t ts = tmem_S0 + (j & 1) * kTcBN + lane_sel;
+            // the whole score row (128 fp32) goes to registers with ONE TMEM round trip (the first version
+            // read it twice in 16-column steps and was issue-bound: ncu 2700 instr/warp/tile, tensor pipe 8.5 %)
+            uint32_t sv[8][16];
+#pragma unroll
+            for (int c = 0; c < 8; ++c) tmem_ld16(ts + c * 16, sv[c]);
+            tmem_ld_wait();
+            const bool diag = kv0 + kTcBN - 1 > off + m0;  // tile touches the causal boundary (CTA-uniform)
+            if (diag) {
+#pragma unroll
+                for (int c = 0; c < 8; ++c)
+#pragma unroll
+                    for (int i = 0; i < 16; ++i)
+                        if (kv0 + c * 16 + i > limit) sv[c][i] = 0xff800000u;  // -inf
+            }
+            float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};  // independent chains
+#pragma unroll
+            for (int c = 0; c < 8; ++c)
+#pragma unroll
+                for (int i = 0; i < 16; ++i) mx4[i & 3] = fmaxf(mx4[i & 3], __uint_as_float(sv[c][i]));
+            const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+            const float mn = fmaxf(m_run, mx);
+            const float mref = mn == -INFINITY ? 0.f : mn * scale_log2;
+            const float corr = ex2_approx(m_run * scale_log2 - mref);  // first tile: 2^-inf = 0
+            m_run = mn;
+            // P = 2^(s*scale - m) packed to bf16 in place (register i of chunk c holds columns 16c+2i, +1)
+            float ls4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int c = 0; c < 8; ++c)
+#pragma unroll
+                for (int i = 0; i < 16; i += 2) {
+                    const float p0 = ex2_approx(fmaf(__uint_as_float(sv[c][i]), scale_log2, -mref));
+                    const float p1 = ex2_approx(fmaf(__uint_as_float(sv[c][i + 1]), scale_log2, -mref));
+                    ls4[(i >> 1) & 3] += p0 + p1;
+                    sv[c][i >> 1] = pack_bf16(p0, p1);
+                }
+            const float lsum = (ls4[0] + ls4[1]) + (ls4[2] + ls4[3]);
+            // the previous P.V must have retired before P is overwritten or O is touched
+            if (j > 0) mbar_wait(o_done, (j - 1) & 1);
+            tc_fence_after();
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                uint8_t* prow = sP + (c >> 2) * kAtomBytes + row * 128;
+                const int ch = (c & 3) * 2;  // first of the two 16-byte chunks of these 16 columns
+                *reinterpret_cast<uint4*>(prow + ((ch ^ (row & 7)) << 4)) =
+                    make_uint4(sv[c][0], sv[c][1], sv[c][2], sv[c][3]);
+                *reinterpret_cast<uint4*>(prow + (((ch + 1) ^ (row & 7)) << 4)) =
+                    make_uint4(sv[c][4], sv[c][5], sv[c][6], sv[c][7]);
+            }
+            l_run = l_run * corr + lsum;
+            // rescale O only if some row of this warp moved its maximum (tcgen05.ld/st are warp-wide)
+            if (j > 0 && __any_sync(0xffffffffu, corr != 1.f)) {
+#pragma unroll 1
+                for (int c = 0; c < kTcD; c += 16) {
+                    uint32_t v[16];
+                    tmem_ld16(tmem_O + lane_sel + c, v);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) * corr);
+                    tmem_st16(tmem_O + lane_sel + c, v);
+                }
+                tmem_st_wait();
+            }
+            // keys past the context in the last tile: their V rows are stale page contents or never-loaded
+            // shared memory; P is 0 there but 0 * NaN would poison O, so clear those rows
+            if (kv0 + kTcBN > ctx) {
+                mbar_wait(&v_full[j & 1], (j >> 1) & 1);
+                const int valid = ctx - kv0;
+                if (row >= valid) {
+                    uint8_t* vrow = sV + (j & 1) * kTileBytes + row * 128;
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        *reinterpret_cast<uint4*>(vrow + i * 16) = make_uint4(0, 0, 0, 0);
+                        *reinterpret_cast<uint4*>(vrow + kAtomBytes + i * 16) = make_uint4(0, 0, 0, 0);
+                    }
+                }
+            }
+            fence_proxy_async();   // generic-proxy smem writes (P, cleared V rows) -> visible to the tensor core
+            tc_fence_before();
+            mbar_arrive_cnt(p_full);
+        }
+        // ---- epilogue: O / l -> bf16
+        mbar_wait(o_done, (n_tiles - 1) & 1);
+        tc_fence_after();
+        const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
+        __nv_bfloat16* orow = out + (static_cast<long long>(q_begin + qpos) * Hq + h) * kTcD;
+#pragma unroll 1
+        for (int c = 0; c < kTcD; c += 16) {
+            uint32_t v[16];
+            tmem_ld16(tmem_O + lane_sel + c, v);
+            tmem_ld_wait();
+            if (qpos < n_q) {
+                uint4 a, b;
+                a.x = pack_bf16(__uint_as_float(v[0]) * inv, __uint_as_float(v[1]) * inv);
+                a.y = pack_bf16(__uint_as_float(v[2]) * inv, __uint_as_float(v[3]) * inv);
+                a.z = pack_bf16(__uint_as_float(v[4]) * inv, __uint_as_float(v[5]) * inv);
+                a.w = pack_bf16(__uint_as_float(v[6]) * inv, __uint_as_float(v[7]) * inv);
+                b.x = pack_bf16(__uint_as_float(v[8]) * inv, __uint_as_float(v[9]) * inv);
+                b.y = pack_bf16(__uint_as_float(v[10]) * inv, __uint_as_float(v[11]) * inv);
+                b.z = pack_bf16(__uint_as_float(v[12]) * inv, __uint_as_float(v[13]) * inv);
+                b.w = pack_bf16(__uint_as_float(v[14]) * inv, __uint_as_float(v[15]) * inv);
+                *reinterpret_cast<uint4*>(orow + c) = a;
+                *reinterpret_cast<uint4*>(orow + c + 8) = b;
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc<512>(tmem_base);
+}
+
+// ---- host: cached TMA descriptors (the runner calls with the same buffers every step) ----------------------
+typedef CUresult (*EncodeTiledFn2)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+struct MapKey {
+    const void* base;
+    long long rows, cols;
+    int box_rows;
+    CUtensorMap map;
+};
+
+static int cached_map(const void* base, long long rows, long long cols, int box_rows, CUtensorMap* out) {
+    static std::mutex mu;
+    static std::vector<MapKey> cache;
+    static EncodeTiledFn2 fn = nullptr;
+    std::lock_guard<std::mutex> lock(mu);
+    for (const MapKey& k : cache)
+        if (k.base == base && k.rows == rows && k.cols == cols && k.box_rows == box_rows) {
+            *out = k.map;
+            return ATX_OK;
+        }
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess) {
+            set_error("cuTensorMapEncodeTiled not available from the driver");
+            return ATX_ERR_CUDA;
+        }
+        fn = reinterpret_cast<EncodeTiledFn2>(p);
+    }
+    MapKey k = {base, rows, cols, box_rows, {}};
+    cuuint64_t dims[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
+    cuuint64_t strides[1] = {static_cast<cuuint64_t>(cols) * 2};
+    cuuint32_t box[2] = {64, static_cast<cuuint32_t>(box_rows)};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(&k.map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled failed (CUresult %d) rows=%lld cols=%lld", static_cast<int>(r), rows, cols);
+        return ATX_ERR_CUDA;
+    }
+    if (cache.size() >= 512) cache.erase(cache.begin());
+    cache.push_back(k);
+    *out = k.map;
+    return ATX_OK;
+}
+
+int launch_prefill_tc(const void* q, const void* kc, const void* vc, const int* bt, const int* cu_q, const int* ctx,
+                      void* out, int S, int max_q_len, long long total_q, long long num_blocks, int Hq, int Hkv,
+                      int max_blocks, float scale, int flags, cudaStream_t stream) {
+    CUtensorMap tmQ, tmK, tmV;
+    int rc = cached_map(q, total_q, static_cast<long long>(Hq) * kTcD, kTcBM, &tmQ);
+    if (rc == ATX_OK) rc = cached_map(kc, num_blocks * Hkv * kTcPage, kTcD, kTcPage, &tmK);
+    if (rc == ATX_OK) rc = cached_map(vc, num_blocks * Hkv * kTcPage, kTcD, kTcPage, &tmV);
+    if (rc != ATX_OK) return rc;
+    static bool attr_done[64] = {false};
+    int dev = 0;
+    ATX_CUDA(cudaGetDevice(&dev));
+    if (dev >= 0 && dev < 64 && !attr_done[dev]) {
+        ATX_CUDA(cudaFuncSetAttribute(attn_prefill_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmem));
+        attr_done[dev] = true;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = (flags & ATX_FLAG_PDL) ? 1 : 0;
+    cfg.gridDim = dim3(static_cast<unsigned>((max_q_len + kTcBM - 1) / kTcBM), static_cast<unsigned>(Hq),
+                       static_cast<unsigned>(S));
+    cfg.blockDim = dim3(kTcThreads);
+    cfg.dynamicSmemBytes = kTcSmem;
+    cfg.stream = stream;
+    ATX_CUDA(cudaLaunchKernelEx(&cfg, attn_prefill_tc_kernel, tmQ, tmK, tmV, bt, cu_q, ctx,
+                                reinterpret_cast<__nv_bfloat16*>(out), Hq, Hkv, max_blocks,
+                                scale * 1.4426950408889634f));
+    return ATX_OK;
+}
+
+}  // namespace atx
