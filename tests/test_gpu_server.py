@@ -42,7 +42,10 @@ def test_chat_runs_on_the_gpu_and_is_deterministic_at_temperature_zero(live):
         r = await client.post("/v1/completions", json=body)
         return r.status, await r.json()
     body = {"prompt": "The quick brown fox", "max_tokens": 12, "temperature": 0}
-    (s1, a), (s2, b) = loop.run_until_complete(asyncio.gather(post(body), post(body)))
+
+    async def both():
+        return await asyncio.gather(post(body), post(body))
+    (s1, a), (s2, b) = loop.run_until_complete(both())
     assert s1 == s2 == 200
     assert a["choices"][0]["text"] == b["choices"][0]["text"] and len(a["choices"][0]["text"]) > 0
     assert a["usage"] == {"prompt_tokens": 19, "completion_tokens": 12, "total_tokens": 31}
@@ -58,7 +61,10 @@ def test_concurrent_fanout_burst_shares_the_prefix_and_reports_metrics(live):
         r = await client.post("/chat", json={"prompt": shared + f"Worker {i}, go.", "max_tokens": 8},
                               headers={"X-Request-ID": f"w{i}"})
         return r.status, await r.json()
-    res = loop.run_until_complete(asyncio.gather(*[one(i) for i in range(5)]))
+
+    async def burst():
+        return await asyncio.gather(*[one(i) for i in range(5)])
+    res = loop.run_until_complete(burst())
     assert all(st == 200 for st, _ in res)
     for i, (_, body) in enumerate(res):
         m = body["meta"]
