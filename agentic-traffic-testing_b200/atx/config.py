@@ -172,6 +172,7 @@ class EngineConfig:
     enable_prefix_caching: bool = True
     enable_cuda_graphs: bool = True
     use_pdl: bool = True
+    async_scheduling: bool = True   # launch decode step N+1 before the host has read step N's tokens
     device: int = 0
     tp_size: int = 1          # tensor-parallel ranks sharing one model (70B); needs torch.distributed NCCL
     tp_rank: int = 0

@@ -52,6 +52,7 @@ class LLMEngine:
                                    self.mcfg.eos_token_ids)
         self.steps = 0
         self.batch_size_observer: Optional[Callable[[int], None]] = None
+        self._inflight = None   # (plan, launch handle) of a step whose tokens the host has not read yet
 
     def add_request(self, request_id: str, prompt_ids: Seq[int], params: SamplingParams) -> Sequence:
         V = self.mcfg.vocab_size
@@ -74,18 +75,60 @@ class LLMEngine:
         self.scheduler.abort(request_id)
 
     def has_work(self) -> bool:
-        return self.scheduler.has_work()
+        return self._inflight is not None or self.scheduler.has_work()
+
+    def _chain(self, plan):
+        """The decode step that follows `plan` if nothing can change the batch: same sequences, next
+        position. Built BEFORE the host knows plan's tokens so that the GPU never waits for the host
+        (scheduling, staging and the token read-back of step N overlap step N+1). Returns None whenever the
+        ordinary scheduler has to run: prompts in the batch or in the queue, a sequence reaching its length
+        limit, or no KV block left for the next position. A sequence that stops on EOS in step N simply has
+        its row of step N+1 ignored."""
+        from .scheduler import Chunk, StepPlan
+
+        sch = self.scheduler
+        if plan.prefills or not plan.decodes or sch.waiting or plan.preempted:
+            return None
+        if len(plan.decodes) != len(sch.running):
+            return None
+        need = 0
+        for c in plan.decodes:
+            s = c.seq
+            if s.state is not SeqState.RUNNING:
+                return None
+            if s.num_generated + 1 >= s.params.max_tokens or len(s.tokens) + 1 >= sch.max_model_len:
+                return None   # finishes on length with the in-flight token: composition changes
+            need += s.blocks.blocks_needed(c.start + 2)
+        if need > self.allocator.num_free:
+            return None
+        nxt = StepPlan()
+        for c in plan.decodes:
+            c.seq.blocks.ensure_capacity(c.start + 2)
+            nxt.decodes.append(Chunk(c.seq, c.start + 1, 1, True))
+        return nxt
 
     def step(self) -> List[Sequence]:
         """One scheduler + forward pass. Returns sequences that received a token."""
-        plan = self.scheduler.schedule()
-        if plan.empty:
-            return []
-        if self.batch_size_observer is not None:
-            self.batch_size_observer(len(plan.decodes) + len(plan.prefills))
-        sampled = self.runner.execute(plan)
+        if self._inflight is None:
+            plan = self.scheduler.schedule()
+            if plan.empty:
+                return []
+            if self.batch_size_observer is not None:
+                self.batch_size_observer(len(plan.decodes) + len(plan.prefills))
+            self._inflight = (plan, self.runner.launch(plan))
+        plan, handle = self._inflight
+        nxt = None
+        if self.ecfg.async_scheduling:
+            cplan = self._chain(plan)
+            if cplan is not None:
+                if self.batch_size_observer is not None:
+                    self.batch_size_observer(len(cplan.decodes))
+                nxt = (cplan, self.runner.launch(cplan, chained=True))
+        sampled = self.runner.wait(handle)
         self.steps += 1
-        return self.scheduler.commit(plan, sampled)
+        touched = self.scheduler.commit(plan, sampled)
+        self._inflight = nxt
+        return touched
 
     def generate_sync(self, prompts: List[Seq[int]], params: SamplingParams) -> List[List[int]]:
         """Blocking helper for tests and the bench: run the given prompts to completion."""
@@ -208,6 +251,11 @@ class AsyncEngine:
                     if st is None:
                         continue
                     fin = seq.state is SeqState.FINISHED
+                    n_out = seq.num_generated
+                    # every cross-thread wake-up costs the engine thread the GIL: non-streaming callers only
+                    # need the first token (TTFT), an occasional progress mark and the final result
+                    if not (fin or n_out == 1 or seq.params.stream or n_out % 32 == 0):
+                        continue
                     out = seq.output_ids
                     ttft = (seq.first_token_time - seq.arrival) if seq.first_token_time else None
                     self._post(st, RequestOutput(seq.request_id, out, out[-1:], fin, seq.finish_reason,

@@ -61,8 +61,10 @@ def _engine_worker(rank: int, model: str, ecfg: EngineConfig, req, resp) -> None
         try:
             for seq in eng.step():
                 fin = seq.state is SeqState.FINISHED
+                if not (fin or seq.num_generated == 1 or seq.params.stream or seq.num_generated % 32 == 0):
+                    continue
                 out = seq.output_ids
-                resp.send(("out", seq.request_id, out if fin else out[-1:], fin, seq.finish_reason, seq.prompt_len,
+                resp.send(("out", seq.request_id, out, fin, seq.finish_reason, seq.prompt_len,
                            seq.cached_prompt_tokens))
             if eng.steps % 16 == 0:
                 resp.send(("stats", rank, eng.allocator.num_used))
@@ -184,10 +186,7 @@ class ReplicaPool:
                 if st is None:
                     continue
                 loop, q, _, _, acc = st
-                if fin:
-                    acc[:] = toks
-                else:
-                    acc.extend(toks)
+                acc[:] = toks   # replicas send the full id list (sparse updates for non-streaming callers)
                 out = self._RequestOutput(rid, list(acc), list(toks[-1:]), fin, reason, plen, cached, None)
                 loop.call_soon_threadsafe(q.put_nowait, out)
             elif kind == "error":

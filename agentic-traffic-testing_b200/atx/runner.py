@@ -86,7 +86,9 @@ class ModelRunner:
         self.xl = torch.zeros(S, H, dtype=bf, device=dev)
         self.logits = torch.zeros(S, V, dtype=f32, device=dev)
         self.out_ids = torch.zeros(S, dtype=i32, device=dev)
-        self.out_host = torch.zeros(S, dtype=i32).pin_memory()
+        self.out_host = [torch.zeros(S, dtype=i32).pin_memory() for _ in range(2)]  # ping-pong: one step may be in flight
+        self._out_events = [torch.cuda.Event(), torch.cuda.Event()]
+        self._out_flip = 0
         self.rope = rope_table(m, e.max_model_len, dev)
         self.max_splits = 32
         self.ws = torch.zeros(max(1, _cabi.decode_workspace_bytes(S, m.num_attention_heads // tp, m.head_dim,
@@ -342,18 +344,41 @@ class ModelRunner:
         return s
 
     def execute(self, plan: StepPlan) -> Dict[int, int]:
-        """Run one step; returns {Sequence.uid: sampled token id} for every chunk that samples."""
-        with torch.cuda.stream(self.stream):
-            return self._execute(plan)
+        """Run one step and wait for it; returns {Sequence.uid: sampled token id} for every chunk that samples."""
+        h = self.launch(plan)
+        return self.wait(h) if h is not None else {}
 
-    def _execute(self, plan: StepPlan) -> Dict[int, int]:
+    def launch(self, plan: StepPlan, chained: bool = False):
+        """Enqueue one step (staging copies, kernels or graph replay, token read-back) without waiting.
+        `chained`: the step directly follows an in-flight decode step over the SAME sequences in the same
+        order; its input token ids are not known to the host yet and are taken on the device from the
+        previous step's sampler output (the host fills everything else: positions, slots, lengths)."""
+        with torch.cuda.stream(self.stream):
+            return self._launch(plan, chained)
+
+    def wait(self, handle) -> Dict[int, int]:
+        """Block until the step's sampled ids have reached the pinned host buffer."""
+        if handle is None:
+            return {}
+        sampling, n_dec, B, buf, ev = handle
+        if ev is None:
+            return {}
+        ev.synchronize()
+        oh = self.out_host[buf].numpy()
+        out: Dict[int, int] = {}
+        for r, c in enumerate(sampling):
+            slot_r = r if r < n_dec else (B - n_dec) + r
+            out[c.seq.uid] = int(oh[slot_r])
+        return out
+
+    def _launch(self, plan: StepPlan, chained: bool):
         self._h2d_done.synchronize()  # the previous step's staging copies have left the pinned buffer
         hv, bs = self._hv, self.bs
         decs, pfs = plan.decodes, plan.prefills
         n_dec, n_pf = len(decs), len(pfs)
         T_real = n_dec + sum(c.count for c in pfs)
         if T_real == 0:
-            return {}
+            return None
         if T_real > self.Tmax or n_dec + n_pf > self.Smax:
             raise RuntimeError("step exceeds the runner's static capacity")
         # TP steps contain NCCL all-reduces: they capture fine (thread-local capture mode), but the graphs
@@ -371,7 +396,7 @@ class ModelRunner:
         for i, c in enumerate(decs):
             s = c.seq
             p = c.start
-            ids[i] = s.tokens[p]
+            ids[i] = 0 if chained else s.tokens[p]   # chained: filled on the device from the previous step
             pos[i] = p
             tbl = s.blocks.table
             slots[i] = tbl[p // bs] * bs + p % bs
@@ -415,7 +440,7 @@ class ModelRunner:
             hv["temps_f"][slot_r] = s.params.temperature
             hv["top_p_f"][slot_r] = s.params.top_p
             hv["seeds_q"][slot_r] = s.seed
-            hv["steps"][slot_r] = s.num_generated
+            hv["steps"][slot_r] = s.num_generated + (1 if chained else 0)  # the in-flight step adds one token
             k += 1
         for i in range(n_dec, B):
             hv["temps_f"][i] = 0.0
@@ -432,6 +457,9 @@ class ModelRunner:
             self._h2d("dec_bt", n_dec * self.MB)
         if n_pf:
             self._h2d("pf_bt", n_pf * self.MB)
+        if chained:
+            o_ids, _ = self._off["ids"]
+            self.dbuf[o_ids:o_ids + n_dec].copy_(self.out_ids[:n_dec], non_blocking=True)
         self._h2d_done.record()
 
         splits = self.decode_splits(B, max_len)
@@ -454,16 +482,15 @@ class ModelRunner:
             ev1.record()
             self.step_events.append((ev0, ev1, n_dec, T_real - n_dec, sum(c.start + 1 for c in decs)))
 
-        out: Dict[int, int] = {}
+        ev = None
+        buf = self._out_flip
         if n_rows:
-            self.out_host[:n_rows].copy_(self.out_ids[:n_rows], non_blocking=True)
+            self._out_flip ^= 1
+            self.out_host[buf][:n_rows].copy_(self.out_ids[:n_rows], non_blocking=True)
             self.d2h_bytes += 4 * n_rows
-            torch.cuda.current_stream().synchronize()
-            oh = self.out_host.numpy()
-            for r, c in enumerate(sampling):
-                slot_r = r if r < n_dec else (B - n_dec) + r
-                out[c.seq.uid] = int(oh[slot_r])
-        return out
+            ev = self._out_events[buf]
+            ev.record()
+        return (sampling, n_dec, B, buf, ev)
 
     def _capture(self, B: int, splits: int) -> torch.cuda.CUDAGraph:
         """Capture one decode step for batch bucket B. Inputs already sit in dbuf; the warm-up run

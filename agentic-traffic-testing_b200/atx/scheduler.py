@@ -35,6 +35,7 @@ class SamplingParams:
     seed: Optional[int] = None
     ignore_eos: bool = False
     stop_token_ids: Tuple[int, ...] = ()
+    stream: bool = False   # deliver every token to the caller (else: first token, every 32nd, and the last)
 
 
 class SeqState(enum.Enum):

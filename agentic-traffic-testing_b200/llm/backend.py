@@ -181,7 +181,7 @@ class B200Backend:
             temperature=DEFAULT_TEMPERATURE if temperature is None else float(temperature),
             top_p=1.0 if top_p is None else float(top_p),
             max_tokens=int(max_tokens) if max_tokens is not None else LLM_MAX_TOKENS,
-            seed=seed, ignore_eos=bool(ignore_eos))
+            seed=seed, ignore_eos=bool(ignore_eos), stream=on_text is not None)
 
         t0 = time.monotonic()
         last_log = t0

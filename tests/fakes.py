@@ -58,5 +58,5 @@ def fake_replica_worker(rank, model, ecfg, req, resp):
                 continue
             n = params.max_tokens
             for i in range(n):
-                toks = [1000 * rank + i] if i < n - 1 else [1000 * rank + j for j in range(n)]
+                toks = [1000 * rank + j for j in range(i + 1)]
                 resp.send(("out", rid, toks, i == n - 1, "length" if i == n - 1 else None, len(ids), 0))

@@ -23,7 +23,8 @@ def _engine(shape_name, seed, **kw):
     mcfg = model_config_by_name(shape_name)
     ecfg = EngineConfig(max_model_len=kw.pop("max_model_len", 256), max_num_seqs=kw.pop("max_num_seqs", 8),
                         max_num_batched_tokens=kw.pop("max_num_batched_tokens", 64),
-                        num_gpu_blocks=kw.pop("num_gpu_blocks", 96), **kw)
+                        num_gpu_blocks=kw.pop("num_gpu_blocks", 96),
+                        async_scheduling=kw.pop("async_scheduling", False), **kw)   # tests read runner.logits per step
     w = ModelWeights.from_state_dict(mcfg, sd, torch.device("cuda", 0))
     return LLMEngine(ModelSource(mcfg, None, None), ecfg, w), shape, sd
 
@@ -183,6 +184,33 @@ def test_preemption_recompute_is_transparent():
         _decisive_agreement(shape, sd, p, s.output_ids)
         _decisive_agreement(shape, sd, p, w)
     assert sum(s.output_ids == w for s, w in zip(seqs, want)) >= 2
+
+
+def test_async_scheduling_produces_the_same_tokens():
+    """Launching step N+1 before the host has read step N's tokens (device-side token feed) must not
+    change anything: same greedy ids as the synchronous engine, EOS / length stops included."""
+    from atx.scheduler import SamplingParams
+
+    g = torch.Generator().manual_seed(9)
+    prompts = [torch.randint(0, 1000, (20 + 7 * i,), generator=g).tolist() for i in range(5)]
+    lens = [3, 17, 40, 41, 64]
+    outs = []
+    for mode in (False, True):
+        eng, _, _ = _engine("tiny", 11, num_gpu_blocks=128, async_scheduling=mode, max_num_batched_tokens=256)
+        eng.scheduler.eos = {7}   # make EOS stops happen on this random model
+        seqs = [eng.add_request(f"a{i}", p, SamplingParams(temperature=0.0, max_tokens=n)) for i, (p, n) in
+                enumerate(zip(prompts, lens))]
+        late = None
+        steps = 0
+        while eng.has_work():
+            eng.step()
+            steps += 1
+            if steps == 10:   # a request that arrives while a chained step is in flight
+                late = eng.add_request("late", prompts[0][:9], SamplingParams(temperature=0.0, max_tokens=5))
+        outs.append([s.output_ids for s in seqs] + [late.output_ids])
+        assert eng.allocator.num_used == 0 and eng._inflight is None
+        assert all(s.finish_reason in ("stop", "length") for s in seqs)
+    assert outs[0] == outs[1]
 
 
 def test_no_cuda_means_loud_failure(monkeypatch):
