@@ -25,11 +25,11 @@ namespace atx {
 constexpr int kTcBM = 128;   // query rows per CTA
 constexpr int kTcBN = 128;   // keys per tile
 constexpr int kTcD = 128;
-constexpr int kTcThreads = 192;
+constexpr int kTcThreads = 320;   // TMA warp, MMA warp, 8 softmax warps
 constexpr int kTcPage = 16;
 constexpr int kAtomBytes = 128 * 128;            // [128 rows x 64 bf16], 128B-swizzled
 constexpr int kTileBytes = 2 * kAtomBytes;       // [128 x 128] bf16 as two K- (or N-) atoms
-constexpr int kTcSmem = 6 * kTileBytes + 1024 + 256;  // Q, K x2, V x2, P + align + barriers
+constexpr int kTcSmem = 6 * kTileBytes + 1024 + 256 + 1024;  // Q, K x2, V x2, P + align + barriers + max/sum exchange
 
 __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&v)[16]) {
     asm volatile(
@@ -54,6 +54,7 @@ __device__ __forceinline__ uint64_t umma_desc_sw128_mn(uint32_t smem_addr, uint3
     return d;
 }
 __device__ __forceinline__ void mbar_arrive_cnt(uint64_t* bar) { mbar_arrive(bar); }
+__device__ __forceinline__ void softmax_bar_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 __device__ __forceinline__ float ex2_approx(float x) {  // one MUFU op; 2^-inf = 0
     float y;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -108,7 +109,7 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
             mbar_init(&v_empty[i], 1);
             mbar_init(&s_full[i], 1);
         }
-        mbar_init(p_full, 128);
+        mbar_init(p_full, 256);
         mbar_init(o_done, 1);
         fence_barrier_init();
     }
@@ -202,46 +203,52 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
             }
         }
     } else {
-        // ===== softmax / correction / epilogue: thread <-> query row
+        // ===== softmax / correction / epilogue: EIGHT warps, two per TMEM lane quarter. Thread (row, half)
+        // owns keys [64*half, 64*half+64) of its query row: 64 exponentials instead of 128 per thread and two
+        // warps per scheduler to hide MUFU / FMA latency (with four warps the kernel was softmax-bound at
+        // ~3000 cycles per tile against 1024 cycles of MMA). The two halves of a row exchange their partial
+        // maxima through shared memory; the partial sums are only combined at the very end.
         const int quarter = warp & 3;
+        const int half = (warp - 2) >> 2;               // 0 | 1
         const int row = quarter * 32 + lane;            // row inside the tile == TMEM lane
         const int qpos = m0 + row;                      // query index inside this sequence's chunk
         const int limit = off + qpos;                   // last visible key
         const uint32_t lane_sel = static_cast<uint32_t>(quarter * 32) << 16;
+        float* xch = reinterpret_cast<float*>(tmem_slot + 4);  // [2][128] floats after the barriers
         float m_run = -INFINITY, l_run = 0.f;
         for (int j = 0; j < n_tiles; ++j) {
-            const int kv0 = j * kTcBN;
+            const int kv0 = j * kTcBN + half * 64;      // first key of this thread's half
             mbar_wait(&s_full[j & 1], (j >> 1) & 1);
             tc_fence_after();
-            const uint32_t ts = tmem_S0 + (j & 1) * kTcBN + lane_sel;
-            // the whole score row (128 fp32) goes to registers with ONE TMEM round trip (the first version
-            // read it twice in 16-column steps and was issue-bound: ncu 2700 instr/warp/tile, tensor pipe 8.5 %)
-            uint32_t sv[8][16];
+            const uint32_t ts = tmem_S0 + (j & 1) * kTcBN + half * 64 + lane_sel;
+            uint32_t sv[4][16];                          // 64 scores: one TMEM round trip
 #pragma unroll
-            for (int c = 0; c < 8; ++c) tmem_ld16(ts + c * 16, sv[c]);
+            for (int c = 0; c < 4; ++c) tmem_ld16(ts + c * 16, sv[c]);
             tmem_ld_wait();
-            const bool diag = kv0 + kTcBN - 1 > off + m0;  // tile touches the causal boundary (CTA-uniform)
+            const bool diag = j * kTcBN + kTcBN - 1 > off + m0;  // tile touches the causal boundary (CTA-uniform)
             if (diag) {
 #pragma unroll
-                for (int c = 0; c < 8; ++c)
+                for (int c = 0; c < 4; ++c)
 #pragma unroll
                     for (int i = 0; i < 16; ++i)
                         if (kv0 + c * 16 + i > limit) sv[c][i] = 0xff800000u;  // -inf
             }
             float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};  // independent chains
 #pragma unroll
-            for (int c = 0; c < 8; ++c)
+            for (int c = 0; c < 4; ++c)
 #pragma unroll
                 for (int i = 0; i < 16; ++i) mx4[i & 3] = fmaxf(mx4[i & 3], __uint_as_float(sv[c][i]));
-            const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+            const float mx_mine = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+            xch[half * 128 + row] = mx_mine;
+            softmax_bar_sync();
+            const float mx = fmaxf(mx_mine, xch[(half ^ 1) * 128 + row]);
             const float mn = fmaxf(m_run, mx);
             const float mref = mn == -INFINITY ? 0.f : mn * scale_log2;
             const float corr = ex2_approx(m_run * scale_log2 - mref);  // first tile: 2^-inf = 0
             m_run = mn;
-            // P = 2^(s*scale - m) packed to bf16 in place (register i of chunk c holds columns 16c+2i, +1)
             float ls4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-            for (int c = 0; c < 8; ++c)
+            for (int c = 0; c < 4; ++c)
 #pragma unroll
                 for (int i = 0; i < 16; i += 2) {
                     const float p0 = ex2_approx(fmaf(__uint_as_float(sv[c][i]), scale_log2, -mref));
@@ -249,60 +256,60 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
                     ls4[(i >> 1) & 3] += p0 + p1;
                     sv[c][i >> 1] = pack_bf16(p0, p1);
                 }
-            const float lsum = (ls4[0] + ls4[1]) + (ls4[2] + ls4[3]);
+            l_run = l_run * corr + (ls4[0] + ls4[1]) + (ls4[2] + ls4[3]);
             // the previous P.V must have retired before P is overwritten or O is touched
             if (j > 0) mbar_wait(o_done, (j - 1) & 1);
             tc_fence_after();
+            uint8_t* prow = sP + half * kAtomBytes + row * 128;   // this half == one 64-key atom of P
 #pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                uint8_t* prow = sP + (c >> 2) * kAtomBytes + row * 128;
-                const int ch = (c & 3) * 2;  // first of the two 16-byte chunks of these 16 columns
+            for (int c = 0; c < 4; ++c) {
+                const int ch = c * 2;  // the two 16-byte chunks of these 16 keys
                 *reinterpret_cast<uint4*>(prow + ((ch ^ (row & 7)) << 4)) =
                     make_uint4(sv[c][0], sv[c][1], sv[c][2], sv[c][3]);
                 *reinterpret_cast<uint4*>(prow + (((ch + 1) ^ (row & 7)) << 4)) =
                     make_uint4(sv[c][4], sv[c][5], sv[c][6], sv[c][7]);
             }
-            l_run = l_run * corr + lsum;
-            // rescale O only if some row of this warp moved its maximum (tcgen05.ld/st are warp-wide)
+            // rescale this half's 64 columns of O only if some row of the warp moved its maximum
             if (j > 0 && __any_sync(0xffffffffu, corr != 1.f)) {
 #pragma unroll 1
-                for (int c = 0; c < kTcD; c += 16) {
+                for (int c = 0; c < 64; c += 16) {
                     uint32_t v[16];
-                    tmem_ld16(tmem_O + lane_sel + c, v);
+                    tmem_ld16(tmem_O + lane_sel + half * 64 + c, v);
                     tmem_ld_wait();
 #pragma unroll
                     for (int i = 0; i < 16; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) * corr);
-                    tmem_st16(tmem_O + lane_sel + c, v);
+                    tmem_st16(tmem_O + lane_sel + half * 64 + c, v);
                 }
                 tmem_st_wait();
             }
             // keys past the context in the last tile: their V rows are stale page contents or never-loaded
-            // shared memory; P is 0 there but 0 * NaN would poison O, so clear those rows
-            if (kv0 + kTcBN > ctx) {
+            // shared memory; P is 0 there but 0 * NaN would poison O, so clear those rows (dim-atom `half`)
+            if (j * kTcBN + kTcBN > ctx) {
                 mbar_wait(&v_full[j & 1], (j >> 1) & 1);
-                const int valid = ctx - kv0;
+                const int valid = ctx - j * kTcBN;
                 if (row >= valid) {
-                    uint8_t* vrow = sV + (j & 1) * kTileBytes + row * 128;
+                    uint8_t* vrow = sV + (j & 1) * kTileBytes + half * kAtomBytes + row * 128;
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        *reinterpret_cast<uint4*>(vrow + i * 16) = make_uint4(0, 0, 0, 0);
-                        *reinterpret_cast<uint4*>(vrow + kAtomBytes + i * 16) = make_uint4(0, 0, 0, 0);
-                    }
+                    for (int i = 0; i < 8; ++i) *reinterpret_cast<uint4*>(vrow + i * 16) = make_uint4(0, 0, 0, 0);
                 }
             }
             fence_proxy_async();   // generic-proxy smem writes (P, cleared V rows) -> visible to the tensor core
             tc_fence_before();
             mbar_arrive_cnt(p_full);
+            softmax_bar_sync();    // both halves have read this tile's exchanged maxima before the next write
         }
-        // ---- epilogue: O / l -> bf16
+        // ---- epilogue: O / l -> bf16 (each half stores 64 dims of its row)
+        xch[half * 128 + row] = l_run;
+        softmax_bar_sync();
+        const float l_tot = l_run + xch[(half ^ 1) * 128 + row];
         mbar_wait(o_done, (n_tiles - 1) & 1);
         tc_fence_after();
-        const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
-        __nv_bfloat16* orow = out + (static_cast<long long>(q_begin + qpos) * Hq + h) * kTcD;
+        const float inv = l_tot > 0.f ? 1.f / l_tot : 0.f;
+        __nv_bfloat16* orow = out + (static_cast<long long>(q_begin + qpos) * Hq + h) * kTcD + half * 64;
 #pragma unroll 1
-        for (int c = 0; c < kTcD; c += 16) {
+        for (int c = 0; c < 64; c += 16) {
             uint32_t v[16];
-            tmem_ld16(tmem_O + lane_sel + c, v);
+            tmem_ld16(tmem_O + lane_sel + half * 64 + c, v);
             tmem_ld_wait();
             if (qpos < n_q) {
                 uint4 a, b;

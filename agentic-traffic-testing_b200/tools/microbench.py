@@ -98,10 +98,13 @@ if __name__ == "__main__":
     ap.add_argument("what", choices=["gemm", "attn", "prefill", "all"])
     ap.add_argument("--T", type=int, nargs="*", default=[6])
     ap.add_argument("--splits", type=int, nargs="*", default=[0])
+    ap.add_argument("--shapes", default="8b", choices=["8b", "70b_tp8"])
     a = ap.parse_args()
     if a.what in ("gemm", "all"):
+        shapes = None if a.shapes == "8b" else [("qkv", 1280, 8192), ("o", 8192, 1024), ("gate_up", 7168, 8192),
+                                                 ("down", 8192, 3584), ("lm_head", 16032, 8192)]
         for T in a.T:
-            bench_gemm(T, splits_list=tuple(a.splits))
+            bench_gemm(T, shapes=shapes, splits_list=tuple(a.splits))
     if a.what in ("attn", "all"):
         bench_attn()
     if a.what in ("prefill", "all"):
