@@ -242,10 +242,20 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
             xch[half * 128 + row] = mx_mine;
             softmax_bar_sync();
             const float mx = fmaxf(mx_mine, xch[(half ^ 1) * 128 + row]);
-            const float mn = fmaxf(m_run, mx);
-            const float mref = mn == -INFINITY ? 0.f : mn * scale_log2;
-            const float corr = ex2_approx(m_run * scale_log2 - mref);  // first tile: 2^-inf = 0
-            m_run = mn;
+            // Lazy reference update: the exponent reference only moves when some row of this warp saw its
+            // maximum grow by more than 2^8 relative to it (P stays <= 256, exact in fp32 and fine in bf16; l
+            // accumulates against the same reference, so the final O / l is unchanged). Rescaling O in TMEM
+            // costs ~1000 cycles on the critical path and was taken on 97 % of tiles with an eager update.
+            // Both warps of a row quarter see the same maxima, so they take the same branch.
+            const float cand = mx * scale_log2;  // -inf when the row has seen nothing in this tile
+            float corr = 1.f;
+            const bool moved = __any_sync(0xffffffffu, cand > m_run + 8.f);
+            if (moved) {
+                const float mnew = fmaxf(m_run, cand);
+                corr = ex2_approx(m_run - mnew);   // first tile: 2^-inf = 0
+                m_run = mnew;
+            }
+            const float mref = m_run == -INFINITY ? 0.f : m_run;
             float ls4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
             for (int c = 0; c < 4; ++c)
@@ -270,7 +280,7 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
                     make_uint4(sv[c][4], sv[c][5], sv[c][6], sv[c][7]);
             }
             // rescale this half's 64 columns of O only if some row of the warp moved its maximum
-            if (j > 0 && __any_sync(0xffffffffu, corr != 1.f)) {
+            if (j > 0 && moved) {
 #pragma unroll 1
                 for (int c = 0; c < 64; c += 16) {
                     uint32_t v[16];
