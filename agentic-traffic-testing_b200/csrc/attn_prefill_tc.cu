@@ -9,9 +9,11 @@
 //
 // One CTA = 128 query rows of one head. Warp 0: TMA producer (Q once; K and V page by page — a page of one
 // KV head is 16 rows x 256 B, loaded as two 128B-swizzled boxes — into 2-deep rings). Warp 1: the single
-// MMA-issuing thread. Warps 2-5: one thread per query row: read S from TMEM, causal mask, online softmax in
-// registers (no shuffles: a thread owns its row), write P as bf16 into the swizzled A-operand layout,
-// rescale O in TMEM only when some row's running max moved, finally normalise and store.
+// MMA-issuing thread. Warps 2-9: two threads per query row (each owns 64 of the tile's 128 keys; the two
+// halves of a row meet through a small smem exchange): read S from TMEM, causal mask, online softmax in
+// registers, write P as bf16 into the swizzled A-operand layout, rescale O in TMEM only when some row's
+// running max grew by more than 2^8 (lazy reference), finally normalise and store.
+// K runs one tile ahead of V in the producer (K0 K1 V0 K2 V1 ...), each with its own ring and barriers.
 // S is double-buffered in TMEM so QK^T of tile j+1 overlaps the softmax of tile j.
 #include "common.cuh"
 
@@ -29,7 +31,9 @@ constexpr int kTcThreads = 320;   // TMA warp, MMA warp, 8 softmax warps
 constexpr int kTcPage = 16;
 constexpr int kAtomBytes = 128 * 128;            // [128 rows x 64 bf16], 128B-swizzled
 constexpr int kTileBytes = 2 * kAtomBytes;       // [128 x 128] bf16 as two K- (or N-) atoms
-constexpr int kTcSmem = 6 * kTileBytes + 1024 + 256 + 1024;  // Q, K x2, V x2, P + align + barriers + max/sum exchange
+constexpr int kKS = 2;            // K ring depth (3 measured no faster: the kernel is bound by the softmax warps, not by loads)
+constexpr int kVS = 2;            // V ring depth
+constexpr int kTcSmem = (2 + kKS + kVS) * kTileBytes + 1024 + 256 + 1024;  // Q, K ring, V ring, P + align + barriers + exchange
 
 __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&v)[16]) {
     asm volatile(
@@ -70,19 +74,19 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                                ~static_cast<uintptr_t>(1023));
     uint8_t* sQ = smem;
-    uint8_t* sK = smem + kTileBytes;          // 2 stages
-    uint8_t* sV = smem + 3 * kTileBytes;      // 2 stages
-    uint8_t* sP = smem + 5 * kTileBytes;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 6 * kTileBytes);
+    uint8_t* sK = smem + kTileBytes;                      // kKS stages
+    uint8_t* sV = smem + (1 + kKS) * kTileBytes;          // kVS stages
+    uint8_t* sP = smem + (1 + kKS + kVS) * kTileBytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (2 + kKS + kVS) * kTileBytes);
     uint64_t* q_full = bars;            // 1
-    uint64_t* k_full = bars + 1;        // 2
-    uint64_t* k_empty = bars + 3;       // 2
-    uint64_t* v_full = bars + 5;        // 2
-    uint64_t* v_empty = bars + 7;       // 2
-    uint64_t* s_full = bars + 9;        // 2
-    uint64_t* p_full = bars + 11;       // 1
-    uint64_t* o_done = bars + 12;       // 1
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 13);
+    uint64_t* k_full = bars + 1;        // 4 slots reserved
+    uint64_t* k_empty = bars + 5;       // 4
+    uint64_t* v_full = bars + 9;        // 4
+    uint64_t* v_empty = bars + 13;      // 4
+    uint64_t* s_full = bars + 17;       // 2
+    uint64_t* p_full = bars + 19;       // 1
+    uint64_t* o_done = bars + 20;       // 1
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 21);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int s = blockIdx.z, h = blockIdx.y;
@@ -102,13 +106,14 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
         tma_prefetch_desc(&tmK);
         tma_prefetch_desc(&tmV);
         mbar_init(q_full, 1);
-        for (int i = 0; i < 2; ++i) {
+        for (int i = 0; i < 4; ++i) {
             mbar_init(&k_full[i], 1);
             mbar_init(&k_empty[i], 1);
             mbar_init(&v_full[i], 1);
             mbar_init(&v_empty[i], 1);
-            mbar_init(&s_full[i], 1);
         }
+        mbar_init(&s_full[0], 1);
+        mbar_init(&s_full[1], 1);
         mbar_init(p_full, 256);
         mbar_init(o_done, 1);
         fence_barrier_init();
@@ -136,33 +141,43 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
             const int pages = min(kTcBN / kTcPage, (ctx - kv0 + kTcPage - 1) / kTcPage);
             return (j < n_tiles && lane < pages) ? (__ldg(bt + kv0 / kTcPage + lane) * Hkv + g) * kTcPage : -1;
         };
-        int row_next = page_row(0);
+        auto tile_pages = [&](int j) { return min(kTcBN / kTcPage, (ctx - j * kTcBN + kTcPage - 1) / kTcPage); };
+        auto load_k = [&](int j, int row) {
+            const int ks = j % kKS;
+            if (lane == 0) {
+                mbar_wait(&k_empty[ks], ((j / kKS) & 1) ^ 1);
+                mbar_expect_tx(&k_full[ks], tile_pages(j) * kTcPage * 256);   // allocated pages only
+            }
+            __syncwarp();
+            if (row >= 0) {
+                uint8_t* dst = sK + ks * kTileBytes + lane * kTcPage * 128;
+                tma_load_2d(dst, &tmK, &k_full[ks], 0, row, kEvictLast);
+                tma_load_2d(dst + kAtomBytes, &tmK, &k_full[ks], 64, row, kEvictLast);
+            }
+        };
+        auto load_v = [&](int j, int row) {
+            const int vs = j % kVS;
+            if (lane == 0) {
+                mbar_wait(&v_empty[vs], ((j / kVS) & 1) ^ 1);
+                mbar_expect_tx(&v_full[vs], tile_pages(j) * kTcPage * 256);
+            }
+            __syncwarp();
+            if (row >= 0) {
+                uint8_t* dst = sV + vs * kTileBytes + lane * kTcPage * 128;
+                tma_load_2d(dst, &tmV, &v_full[vs], 0, row, kEvictLast);
+                tma_load_2d(dst + kAtomBytes, &tmV, &v_full[vs], 64, row, kEvictLast);
+            }
+        };
+        // K runs one tile ahead of V (QK^T of tile j+1 is issued before P.V of tile j): K0, K1, V0, K2, V1, ...
+        int row_cur = page_row(0);
+        int row_nxt = page_row(1);
+        load_k(0, row_cur);
         for (int j = 0; j < n_tiles; ++j) {
-            const int st = j & 1;
-            const uint32_t ph = (j >> 1) & 1;
-            const int row = row_next;
-            row_next = page_row(j + 1);  // lookup for the next tile is in flight while this one is issued
-            const int pages = min(kTcBN / kTcPage, (ctx - j * kTcBN + kTcPage - 1) / kTcPage);  // allocated pages only
-            if (lane == 0) {
-                mbar_wait(&k_empty[st], ph ^ 1);
-                mbar_expect_tx(&k_full[st], pages * kTcPage * 256);
-            }
-            __syncwarp();
-            if (row >= 0) {
-                uint8_t* dst = sK + st * kTileBytes + lane * kTcPage * 128;
-                tma_load_2d(dst, &tmK, &k_full[st], 0, row, kEvictLast);
-                tma_load_2d(dst + kAtomBytes, &tmK, &k_full[st], 64, row, kEvictLast);
-            }
-            if (lane == 0) {
-                mbar_wait(&v_empty[st], ph ^ 1);
-                mbar_expect_tx(&v_full[st], pages * kTcPage * 256);
-            }
-            __syncwarp();
-            if (row >= 0) {
-                uint8_t* dst = sV + st * kTileBytes + lane * kTcPage * 128;
-                tma_load_2d(dst, &tmV, &v_full[st], 0, row, kEvictLast);
-                tma_load_2d(dst + kAtomBytes, &tmV, &v_full[st], 64, row, kEvictLast);
-            }
+            const int row_nn = page_row(j + 2);   // block-table lookups stay two tiles ahead of their use
+            if (j + 1 < n_tiles) load_k(j + 1, row_nxt);
+            load_v(j, row_cur);
+            row_cur = row_nxt;
+            row_nxt = row_nn;
         }
     } else if (warp == 1) {
         if (elect_one()) {
@@ -170,8 +185,8 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
             constexpr uint32_t idesc_qk = umma_idesc_bf16(kTcBM, kTcBN);                 // A, B K-major
             constexpr uint32_t idesc_pv = umma_idesc_bf16(kTcBM, kTcD) | (1u << 16);      // B (= V) MN-major
             auto issue_qk = [&](int j) {
-                const int st = j & 1;
-                mbar_wait(&k_full[st], (j >> 1) & 1);
+                const int st = j % kKS;
+                mbar_wait(&k_full[st], (j / kKS) & 1);
                 tc_fence_after();
                 const uint32_t qa = smem_u32(sQ), ka = smem_u32(sK + st * kTileBytes);
 #pragma unroll
@@ -187,8 +202,8 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
             issue_qk(0);
             for (int j = 0; j < n_tiles; ++j) {
                 if (j + 1 < n_tiles) issue_qk(j + 1);  // overlaps the softmax of tile j
-                const int st = j & 1;
-                mbar_wait(&v_full[st], (j >> 1) & 1);
+                const int st = j % kVS;
+                mbar_wait(&v_full[st], (j / kVS) & 1);
                 mbar_wait(p_full, j & 1);              // P(j) in smem, O rescaled, tail rows of V cleared
                 tc_fence_after();
                 const uint32_t pa = smem_u32(sP), va = smem_u32(sV + st * kTileBytes);
@@ -295,10 +310,10 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
             // keys past the context in the last tile: their V rows are stale page contents or never-loaded
             // shared memory; P is 0 there but 0 * NaN would poison O, so clear those rows (dim-atom `half`)
             if (j * kTcBN + kTcBN > ctx) {
-                mbar_wait(&v_full[j & 1], (j >> 1) & 1);
+                mbar_wait(&v_full[j % kVS], (j / kVS) & 1);
                 const int valid = ctx - j * kTcBN;
                 if (row >= valid) {
-                    uint8_t* vrow = sV + (j & 1) * kTileBytes + half * kAtomBytes + row * 128;
+                    uint8_t* vrow = sV + (j % kVS) * kTileBytes + half * kAtomBytes + row * 128;
 #pragma unroll
                     for (int i = 0; i < 8; ++i) *reinterpret_cast<uint4*>(vrow + i * 16) = make_uint4(0, 0, 0, 0);
                 }
