@@ -254,7 +254,7 @@ class ModelRunner:
                 n += 1
             project(p_o)
             norm(l.ln2.data_ptr(), xn)
-            ck(lib.atx_gemm_run(p_gu._h, act, I, T, _cabi.GEMM_SWIGLU_BF16, 1, fl, st))  # silu(g)*u in the epilogue
+            ck(lib.atx_gemm_run(p_gu._h, act, I, T, _cabi.GEMM_SWIGLU_BF16, 0, fl, st))  # silu(g)*u in the epilogue
             n += 1
             project(p_down)
         if n_rows:

@@ -35,17 +35,6 @@ constexpr int kKS = 2;            // K ring depth (3 measured no faster: the ker
 constexpr int kVS = 2;            // V ring depth
 constexpr int kTcSmem = (2 + kKS + kVS) * kTileBytes + 1024 + 256 + 1024;  // Q, K ring, V ring, P + align + barriers + exchange
 
-__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&v)[16]) {
-    asm volatile(
-        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
-        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
-        :
-        : "r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
-          "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
-        : "memory");
-}
-__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
-
 // MN-major operand ([K rows][64 contiguous N elements] atoms, 128B swizzle): LBO = distance between the
 // N-atoms, SBO = distance between groups of 8 K-rows (cute::UMMA canonical Major-MN SW128 layout).
 __device__ __forceinline__ uint64_t umma_desc_sw128_mn(uint32_t smem_addr, uint32_t lbo_bytes) {

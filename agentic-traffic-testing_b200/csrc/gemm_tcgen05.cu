@@ -44,6 +44,21 @@ struct GemmCfg {
     static constexpr uint32_t kTmemCols = TN < 32 ? 32 : TN;
 };
 
+__device__ __forceinline__ void cluster_barrier() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t dsmem_addr(const void* local_ptr, uint32_t cta_rank) {
+    uint32_t remote;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(smem_u32(local_ptr)), "r"(cta_rank));
+    return remote;
+}
+__device__ __forceinline__ float dsmem_ld(uint32_t remote_addr) {
+    float v;
+    asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(remote_addr) : "memory");
+    return v;
+}
+
 template <int TN>
 __global__ void __launch_bounds__(kGemmThreads)
 gemm_wt_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmX,
@@ -161,7 +176,50 @@ gemm_wt_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
         mbar_wait(accum_bar, 0);
         tc_fence_after();
         pdl_wait();  // `out` may be the residual stream written by the upstream grid
-        if (mode == ATX_GEMM_SWIGLU_BF16) {
+        if (mode == ATX_GEMM_SWIGLU_BF16 && gridDim.z > 1) {
+            // Split-K with a nonlinear epilogue: the gridDim.z CTAs of this tile form ONE thread-block
+            // cluster (launch attribute). CTAs 1.. park their partial accumulator in their own (idle) stage
+            // buffers, the leader pulls them through distributed shared memory in a fixed order, folds
+            // them into its TMEM accumulator and runs the ordinary SwiGLU epilogue: no workspace, no
+            // atomics, bit-reproducible sums. The second cluster barrier keeps the peers' shared memory
+            // alive until the leader has read it.
+            float* part = reinterpret_cast<float*>(smem);  // [TN][128]
+            const int row = warp * 32 + lane;
+            const uint32_t tl = tmem_acc + (static_cast<uint32_t>(warp * 32) << 16);
+            if (blockIdx.z != 0) {
+#pragma unroll 1
+                for (int c = 0; c < TN; c += 16) {
+                    if (t0 + c >= T) break;
+                    uint32_t v[16];
+                    tmem_ld16(tl + c, v);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) part[(c + j) * kBM + row] = __uint_as_float(v[j]);
+                }
+            }
+            cluster_barrier();
+            if (blockIdx.z == 0) {
+#pragma unroll 1
+                for (int c = 0; c < TN; c += 16) {
+                    if (t0 + c >= T) break;
+                    uint32_t v[16];
+                    tmem_ld16(tl + c, v);
+                    tmem_ld_wait();
+                    for (uint32_t r = 1; r < gridDim.z; ++r) {
+                        const uint32_t remote = dsmem_addr(part + c * kBM + row, r);
+#pragma unroll
+                        for (int j = 0; j < 16; ++j)
+                            v[j] = __float_as_uint(__uint_as_float(v[j]) + dsmem_ld(remote + j * kBM * 4));
+                    }
+                    tmem_st16(tl + c, v);
+                }
+                tmem_st_wait();
+            }
+            cluster_barrier();
+        }
+        if (mode == ATX_GEMM_SWIGLU_BF16 && blockIdx.z != 0) {
+            // cluster peer: its sum now lives in the leader's accumulator
+        } else if (mode == ATX_GEMM_SWIGLU_BF16) {
             // Rows [0,64) of this tile are gate features, rows [64,128) the matching up features
             // (weights interleaved in 64-row groups at load time): act = silu(gate) * up, bf16.
             // The halves cross between warps 0-1 (gate lanes) and warps 2-3 (up lanes) through the
@@ -552,8 +610,9 @@ static int launch_gemm(const atx_gemm_plan* p, int ti, void* out, long long ldo,
     const int zs = (kb_total + kb_per - 1) / kb_per;
     int stages = kb_per < Cfg::kStages ? kb_per : Cfg::kStages;
     // the fused-SwiGLU epilogue parks half a tile in the stage buffers: keep them large enough
+    // (a whole fp32 tile when the split-K cluster parks partial sums there)
     if (mode == ATX_GEMM_SWIGLU_BF16) {
-        const int need = (TN * 64 * 4 + Cfg::kStageBytes - 1) / Cfg::kStageBytes;
+        const int need = (TN * (zs > 1 ? kBM : 64) * 4 + Cfg::kStageBytes - 1) / Cfg::kStageBytes;
         if (stages < need) stages = need;
     }
     const int smem_bytes = stages * Cfg::kStageBytes + 1024 + 256;
@@ -563,11 +622,22 @@ static int launch_gemm(const atx_gemm_plan* p, int ti, void* out, long long ldo,
     cfg.blockDim = dim3(kGemmThreads);
     cfg.dynamicSmemBytes = smem_bytes;
     cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchAttribute attr[2];
+    int na = 0;
+    if (pdl) {
+        attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[na].val.programmaticStreamSerializationAllowed = 1;
+        ++na;
+    }
+    if (mode == ATX_GEMM_SWIGLU_BF16 && zs > 1) {  // the K-splits of one tile are one cluster (DSMEM reduction)
+        attr[na].id = cudaLaunchAttributeClusterDimension;
+        attr[na].val.clusterDim.x = 1;
+        attr[na].val.clusterDim.y = 1;
+        attr[na].val.clusterDim.z = static_cast<unsigned>(zs);
+        ++na;
+    }
     cfg.attrs = attr;
-    cfg.numAttrs = pdl ? 1 : 0;
+    cfg.numAttrs = na;
     ATX_CUDA(cudaLaunchKernelEx(&cfg, gemm_wt_kernel<TN>, p->tmW, p->tmX[ti], out, ldo, T,
                                 static_cast<int>(p->N), kb_total, kb_per, mode, p->w_evict_first,
                                 pdl ? tl_l2_prefetch_kb : 0, stages));
@@ -666,9 +736,21 @@ int atx_gemm_run(const atx_gemm_plan* p, void* out, long long ldo, int T, int mo
     ATX_REQUIRE(mode >= ATX_GEMM_STORE_F32 && mode <= ATX_GEMM_SWIGLU_BF16, "atx_gemm_run: bad mode %d", mode);
     ATX_REQUIRE(ldo >= (mode == ATX_GEMM_SWIGLU_BF16 ? p->N / 2 : p->N), "atx_gemm_run: ldo=%lld too small for N=%lld", ldo, p->N);
     ATX_REQUIRE(mode != ATX_GEMM_SWIGLU_BF16 || p->N % 128 == 0, "atx_gemm_run: SWIGLU mode needs N %% 128 == 0");
-    if (splits <= 0) splits = (mode == ATX_GEMM_ADD_F32) ? atx_gemm_auto_splits(p->N, p->K, T) : 1;
-    ATX_REQUIRE(splits == 1 || mode == ATX_GEMM_ADD_F32,
-                "atx_gemm_run: split-K (%d) needs ATX_GEMM_ADD_F32 into a zeroed or residual buffer", splits);
+    if (splits <= 0) {
+        splits = 1;
+        if (mode == ATX_GEMM_ADD_F32) splits = atx_gemm_auto_splits(p->N, p->K, T);
+        if (mode == ATX_GEMM_SWIGLU_BF16 && T <= 64) {  // cluster split-K: a power of two, at most 8 CTAs
+            const int want = atx_gemm_auto_splits(p->N, p->K, T);
+            while (splits * 2 <= want && splits * 2 <= 8 && (p->K / kBK) % (splits * 2) == 0) splits *= 2;
+        }
+    }
+    ATX_REQUIRE(splits == 1 || mode == ATX_GEMM_ADD_F32 || mode == ATX_GEMM_SWIGLU_BF16,
+                "atx_gemm_run: split-K (%d) needs ATX_GEMM_ADD_F32 into a zeroed or residual buffer, or "
+                "ATX_GEMM_SWIGLU_BF16 (cluster reduction)", splits);
+    ATX_REQUIRE(mode != ATX_GEMM_SWIGLU_BF16 || splits == 1 ||
+                    (T <= 64 && splits <= 8 && (splits & (splits - 1)) == 0 && (p->K / kBK) % splits == 0),
+                "atx_gemm_run: SWIGLU split-K needs T <= 64 and splits in {2,4,8} dividing K/64 (got T=%d splits=%d)",
+                T, splits);
     const int pdl = (flags & ATX_FLAG_PDL) ? 1 : 0;
     // per-call L2 prefetch depth (k-blocks) in bits 8..15 of flags overrides the process-wide default
     tl_l2_prefetch_kb = ((flags >> 8) & 0xff) ? ((flags >> 8) & 0xff) : g_l2_prefetch_kb;

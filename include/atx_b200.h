@@ -53,12 +53,14 @@ typedef struct atx_gemm_plan atx_gemm_plan;
 #define ATX_GEMM_STORE_BF16 2 /* out bf16 = round(acc)                                     */
 /* Fused SwiGLU (modeling_llama.py:182-184): W holds gate and up rows INTERLEAVED in groups of 64
  * (rows [128j, 128j+64) = gate[64j..], rows [128j+64, 128j+128) = up[64j..]); out is bf16
- * [T, N/2] with out[t, 64j+i] = silu(acc_gate) * acc_up. No split-K. */
+ * [T, N/2] with out[t, 64j+i] = silu(acc_gate) * acc_up. Split-K (T <= 64, splits in {2,4,8} dividing
+ * K/64) runs the splits of a tile as one thread-block cluster and sums them through distributed shared
+ * memory in a fixed order: no workspace, no atomics, repeatable bit for bit. */
 #define ATX_GEMM_SWIGLU_BF16 3
 int atx_gemm_plan_create(atx_gemm_plan** plan, const void* W, long long N, long long K, const void* X,
                          long long T_cap, long long ldx);
 void atx_gemm_plan_destroy(atx_gemm_plan* plan);
-/* splits: K partitions (>=1); 0 = choose (only ADD mode may split). ldo: out row pitch in elements. */
+/* splits: K partitions (>=1); 0 = choose (ADD and SWIGLU modes may split). ldo: out row pitch in elements. */
 int atx_gemm_run(const atx_gemm_plan* plan, void* out, long long ldo, int T, int mode, int splits,
                  int flags, atx_stream_t stream);
 int atx_gemm_auto_splits(long long N, long long K, int T);

@@ -90,7 +90,40 @@ def test_gemm_fused_swiglu_epilogue(cabi, T, I, K):
     err = (out.float().cpu() - want).abs()
     assert torch.all(err <= 2 ** -7 * want.abs() + 1e-3), float(err.max())
     with pytest.raises(cabi.AtxError, match="split-K"):
-        plan.run(out, T, cabi.GEMM_SWIGLU_BF16, 2)
+        plan.run(out, T, cabi.GEMM_SWIGLU_BF16, 3)   # cluster split-K takes 2, 4 or 8 only
+    if T > 64:
+        with pytest.raises(cabi.AtxError, match="split-K"):
+            plan.run(out, T, cabi.GEMM_SWIGLU_BF16, 2)
+
+
+@pytest.mark.parametrize("T,I,K,splits", [(1, 128, 512, 2), (6, 448, 1024, 4), (16, 192, 2048, 8), (17, 256, 512, 8),
+                                          (32, 3584, 8192, 0), (33, 320, 1024, 2), (64, 128, 512, 4)])
+def test_gemm_swiglu_cluster_split_k(cabi, T, I, K, splits):
+    """SwiGLU with split-K: the K-splits of a tile are one thread-block cluster, partial sums meet in the
+    leader's TMEM through distributed shared memory. Same result as the unsplit kernel up to fp32 summation
+    order (compared in bf16), NaN-poisoned destination fully overwritten, repeatable bit for bit."""
+    from atx.weights import interleave_gate_up
+
+    g = torch.Generator().manual_seed(11 * T + I + K)
+    x = _bf16(torch.randn(T, K, generator=g))
+    wg = _bf16(torch.randn(I, K, generator=g) * 0.05)
+    wu = _bf16(torch.randn(I, K, generator=g) * 0.05)
+    xb = torch.full((max(T, 8) + 3, K), float("nan"), dtype=torch.bfloat16, device="cuda")
+    xb[:T] = x.cuda()
+    plan = cabi.GemmPlan(interleave_gate_up(wg, wu).cuda().contiguous(), xb)
+    outs = []
+    for _ in range(2):
+        out = torch.full((T, I), float("nan"), dtype=torch.bfloat16, device="cuda")
+        plan.run(out, T, cabi.GEMM_SWIGLU_BF16, splits)
+        outs.append(out.clone())
+    assert torch.equal(outs[0], outs[1])
+    want = R.swiglu(x.float() @ wg.float().T, x.float() @ wu.float().T)
+    err = (outs[0].float().cpu() - want).abs()
+    assert torch.all(err <= 2 ** -7 * want.abs() + 1e-3), float(err.max())
+    one = torch.empty_like(outs[0])
+    plan.run(one, T, cabi.GEMM_SWIGLU_BF16, 1)
+    d = (one.float() - outs[0].float()).abs()
+    assert torch.all(d <= 2 ** -7 * one.float().abs() + 1e-3), float(d.max())
 
 
 def test_gemm_rows_beyond_T_do_not_leak(cabi):
