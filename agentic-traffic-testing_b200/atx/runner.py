@@ -158,6 +158,7 @@ class ModelRunner:
         self._h2d_done = torch.cuda.Event()
         self.flags = _cabi.FLAG_PDL if e.use_pdl else 0
         self.lib.atx_gemm_set_l2_prefetch(int(os.environ.get("ATX_L2_PREFETCH_KB", "0")))
+        self.tp_l2_prefetch_kb = int(os.environ.get("ATX_TP_L2_PREFETCH_KB", "0"))
         self.scale = float(m.head_dim) ** -0.5
         self.launches_last_step = 0
         self.kernel_launches = 0  # cumulative count of our kernels launched (graph replays included)
@@ -192,6 +193,9 @@ class ModelRunner:
         dp = self._dp
         h, xn, qkv, q, attn, act = (t.data_ptr() for t in (self.h, self.xn, self.qkv, self.q, self.attn, self.act))
         fused = tp > 1 and self.fused_ar and T <= self.FUSED_AR_MAX_T
+        # GEMMs that follow a fused all-reduce sit idle behind a cross-GPU barrier while HBM is idle too: let
+        # them pull their weight slices into L2 before they wait (per-call ATX_FLAG_L2_PREFETCH)
+        fl_ar = fl | ((self.tp_l2_prefetch_kb & 0xFF) << 8) if (fused and fl) else fl
         if tp == 1:
             targets = (h, h)                      # projections add straight into the residual stream
         elif fused:
@@ -235,10 +239,10 @@ class ModelRunner:
             kc, vc = self.k_cache[li].data_ptr(), self.v_cache[li].data_ptr()
             if sp_qkv > 1:   # split-K accumulates into qkv: the norm kernel's spare CTAs clear it
                 norm(l.ln1.data_ptr(), xn, qkv, T * qkv_size * 4)
-                ck(lib.atx_gemm_run(p_qkv._h, qkv, qkv_size, T, _cabi.GEMM_ADD_F32, sp_qkv, fl, st))
+                ck(lib.atx_gemm_run(p_qkv._h, qkv, qkv_size, T, _cabi.GEMM_ADD_F32, sp_qkv, fl_ar, st))
             else:
                 norm(l.ln1.data_ptr(), xn)
-                ck(lib.atx_gemm_run(p_qkv._h, qkv, qkv_size, T, _cabi.GEMM_STORE_F32, 1, fl, st))
+                ck(lib.atx_gemm_run(p_qkv._h, qkv, qkv_size, T, _cabi.GEMM_STORE_F32, 1, fl_ar, st))
             ck(lib.atx_rope_kv_write(qkv, dp["pos"], dp["slots"], self.rope.data_ptr(), q, kc, vc, T, Hq, Hkv, D,
                                      self.bs, fl, st))
             n += 2
@@ -254,7 +258,7 @@ class ModelRunner:
                 n += 1
             project(p_o)
             norm(l.ln2.data_ptr(), xn)
-            ck(lib.atx_gemm_run(p_gu._h, act, I, T, _cabi.GEMM_SWIGLU_BF16, 0, fl, st))  # silu(g)*u in the epilogue
+            ck(lib.atx_gemm_run(p_gu._h, act, I, T, _cabi.GEMM_SWIGLU_BF16, 0, fl_ar, st))  # silu(g)*u in the epilogue
             n += 1
             project(p_down)
         if n_rows:

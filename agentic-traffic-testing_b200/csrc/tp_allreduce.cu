@@ -23,7 +23,7 @@
 namespace atx {
 
 constexpr int kArThreads = 512;
-constexpr int kArMaxVec = 4;   // float4 per thread -> H <= 8192
+constexpr int kArMaxCluster = 8;   // CTAs per token row, one float4 per thread -> H <= 16384
 constexpr int kArMaxRanks = 8;
 
 struct ArArgs {
@@ -48,19 +48,37 @@ __device__ __forceinline__ float4 ld_peer_f4(const float* p) {
     return v;
 }
 
+__device__ __forceinline__ void ar_cluster_barrier() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ float ar_dsmem_ld(const float* local_ptr, uint32_t cta_rank) {
+    uint32_t remote;
+    float v;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(smem_u32(local_ptr)), "r"(cta_rank));
+    asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(remote) : "memory");
+    return v;
+}
+
+// A token row is split over a cluster of C CTAs (C = H / 2048, so a thread owns ONE float4 of the row): all of
+// a thread's peer loads (world of them) are issued back to back and the whole [T, H] x world message is in
+// flight in a single NVLink round trip instead of one round trip per 2048 columns. The row's sum of squares
+// crosses the cluster through distributed shared memory.
 __global__ void __launch_bounds__(kArThreads)
 allreduce_add_rmsnorm_kernel(ArArgs a, float* __restrict__ x, float* __restrict__ clear_buf, int clear_rows,
                              int* __restrict__ state, int rank, int world, const int* __restrict__ rows,
                              const uint2* __restrict__ w, uint2* __restrict__ out, int T, int H, float eps,
-                             uint4* __restrict__ zero_ptr, long long zero_vecs) {
+                             uint4* __restrict__ zero_ptr, long long zero_vecs, int C) {
     __shared__ float red[kArThreads / 32];
+    __shared__ float css;   // this CTA's share of the row's sum of squares
     pdl_launch_dependents();
     pdl_wait();  // this rank's own GEMM has finished adding into its partial buffer
     const int epoch = *reinterpret_cast<volatile int*>(state) + 1;  // same in every CTA: bumped by the last CTA out
-    if (blockIdx.x >= T) {
-        const long long nb = gridDim.x - T;
-        for (long long i = static_cast<long long>(blockIdx.x - T) * blockDim.x + threadIdx.x; i < zero_vecs;
-             i += nb * blockDim.x)
+    const int t = blockIdx.x / C, c = blockIdx.x % C;   // cluster = the C CTAs of one row
+    if (t >= T) {
+        const long long nb = gridDim.x - static_cast<long long>(T) * C;
+        for (long long i = (static_cast<long long>(blockIdx.x) - static_cast<long long>(T) * C) * blockDim.x + threadIdx.x;
+             i < zero_vecs; i += nb * blockDim.x)
             zero_ptr[i] = make_uint4(0, 0, 0, 0);
     } else {
         // ---- cross-GPU barrier: announce, then wait for every rank's announcement of this round
@@ -75,55 +93,63 @@ allreduce_add_rmsnorm_kernel(ArArgs a, float* __restrict__ x, float* __restrict_
         }
         __syncthreads();
 
-        const int t = blockIdx.x;
         const int r = rows ? rows[t] : t;
-        const int nv = H / 4;
+        const int nv = H / 4, per = (nv + C - 1) / C;
+        const int i = c * per + threadIdx.x;
+        const bool ok = threadIdx.x < per && i < nv;
         float4* xr = reinterpret_cast<float4*>(x + static_cast<long long>(r) * H);
-        float4 v[kArMaxVec];
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
         float ss = 0.f;
+        if (ok) {
+            float4 q[kArMaxRanks];
 #pragma unroll
-        for (int j = 0; j < kArMaxVec; ++j) {
-            const int i = threadIdx.x + j * kArThreads;
-            if (i < nv) {
-                float4 acc = xr[i];
+            for (int p = 0; p < kArMaxRanks; ++p)
+                if (p < world) q[p] = ld_peer_f4(a.part[p] + static_cast<long long>(r) * H + 4 * i);
+            acc = xr[i];
 #pragma unroll
-                for (int p = 0; p < kArMaxRanks; ++p) {
-                    if (p < world) {
-                        const float4 q = ld_peer_f4(a.part[p] + static_cast<long long>(r) * H + 4 * i);
-                        acc.x += q.x; acc.y += q.y; acc.z += q.z; acc.w += q.w;
-                    }
+            for (int p = 0; p < kArMaxRanks; ++p) {   // fixed rank order: every rank computes the same sum
+                if (p < world) {
+                    acc.x += q[p].x; acc.y += q[p].y; acc.z += q[p].z; acc.w += q[p].w;
                 }
-                v[j] = acc;
-                if (!rows) xr[i] = acc;  // the residual stream now includes the reduced projection
-                ss += acc.x * acc.x + acc.y * acc.y + acc.z * acc.z + acc.w * acc.w;
             }
+            if (!rows) xr[i] = acc;  // the residual stream now includes the reduced projection
+            ss = acc.x * acc.x + acc.y * acc.y + acc.z * acc.z + acc.w * acc.w;
         }
         ss = warp_sum(ss);
         if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
         __syncthreads();
-        float tot = 0.f;
+        if (threadIdx.x == 0) {
+            float tot = 0.f;
 #pragma unroll
-        for (int i = 0; i < kArThreads / 32; ++i) tot += red[i];
+            for (int k = 0; k < kArThreads / 32; ++k) tot += red[k];
+            css = tot;
+        }
+        float tot;
+        if (C > 1) {
+            ar_cluster_barrier();
+            tot = 0.f;
+            for (int k = 0; k < C; ++k) tot += ar_dsmem_ld(&css, static_cast<uint32_t>(k));
+        } else {
+            __syncthreads();
+            tot = css;
+        }
         const float rs = rsqrtf(tot / static_cast<float>(H) + eps);
-        uint2* orow = out + static_cast<long long>(t) * nv;
-#pragma unroll
-        for (int j = 0; j < kArMaxVec; ++j) {
-            const int i = threadIdx.x + j * kArThreads;
-            if (i < nv) {
-                const uint2 wv = __ldg(w + i);
-                uint2 o;
-                o.x = pack_bf16(bf16lo(wv.x) * (v[j].x * rs), bf16hi(wv.x) * (v[j].y * rs));
-                o.y = pack_bf16(bf16lo(wv.y) * (v[j].z * rs), bf16hi(wv.y) * (v[j].w * rs));
-                orow[i] = o;
-            }
+        if (ok) {
+            const uint2 wv = __ldg(w + i);
+            uint2 o;
+            o.x = pack_bf16(bf16lo(wv.x) * (acc.x * rs), bf16hi(wv.x) * (acc.y * rs));
+            o.y = pack_bf16(bf16lo(wv.y) * (acc.z * rs), bf16hi(wv.y) * (acc.w * rs));
+            out[static_cast<long long>(t) * nv + i] = o;
         }
         // the other ping-pong buffer was fully read by every peer in the previous round: hand it back clean
         if (clear_buf) {
-            for (int rr = blockIdx.x; rr < clear_rows; rr += T) {
-                float4* c = reinterpret_cast<float4*>(clear_buf + static_cast<long long>(rr) * H);
-                for (int i = threadIdx.x; i < nv; i += kArThreads) c[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-            }
+            const long long cv = static_cast<long long>(clear_rows) * nv;
+            float4* cb = reinterpret_cast<float4*>(clear_buf);
+            for (long long k = static_cast<long long>(blockIdx.x) * kArThreads + threadIdx.x; k < cv;
+                 k += static_cast<long long>(T) * C * kArThreads)
+                cb[k] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
+        if (C > 1) ar_cluster_barrier();   // peers may still be reading css
     }
     // ---- last CTA out publishes the round number for the next call
     __syncthreads();
@@ -151,8 +177,9 @@ int atx_allreduce_add_rmsnorm(float* x, const void* const* part_ptrs, void* cons
     ATX_REQUIRE(x && part_ptrs && flag_ptrs && state && w && out, "atx_allreduce_add_rmsnorm: null pointer");
     ATX_REQUIRE(world >= 2 && world <= kArMaxRanks && rank >= 0 && rank < world,
                 "atx_allreduce_add_rmsnorm: world=%d (2..%d), rank=%d", world, kArMaxRanks, rank);
-    ATX_REQUIRE(T > 0 && H > 0 && H % 4 == 0 && H <= kArThreads * kArMaxVec * 4,
-                "atx_allreduce_add_rmsnorm: bad shape T=%d H=%d (H %% 4 == 0, H <= %d)", T, H, kArThreads * kArMaxVec * 4);
+    ATX_REQUIRE(T > 0 && H > 0 && H % 4 == 0 && H <= kArThreads * kArMaxCluster * 4,
+                "atx_allreduce_add_rmsnorm: bad shape T=%d H=%d (H %% 4 == 0, H <= %d)", T, H,
+                kArThreads * kArMaxCluster * 4);
     ATX_REQUIRE(zero_bytes >= 0 && zero_bytes % 16 == 0 && (zero_bytes == 0 || zero_ptr),
                 "atx_allreduce_add_rmsnorm: zero_bytes=%lld must be a non-negative multiple of 16 with a buffer",
                 zero_bytes);
@@ -165,18 +192,32 @@ int atx_allreduce_add_rmsnorm(float* x, const void* const* part_ptrs, void* cons
     const long long zv = zero_bytes / 16;
     long long zb = (zv + kArThreads * 8 - 1) / (kArThreads * 8);
     if (zb > 1024) zb = 1024;
+    int C = 1;   // power of two so that the cluster shape is portable
+    while (C * kArThreads * 4 < H) C *= 2;
     cudaLaunchConfig_t cfg = {};
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchAttribute attr[2];
+    int na = 0;
+    if (flags & ATX_FLAG_PDL) {
+        attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[na].val.programmaticStreamSerializationAllowed = 1;
+        ++na;
+    }
+    if (C > 1) {
+        attr[na].id = cudaLaunchAttributeClusterDimension;
+        attr[na].val.clusterDim.x = static_cast<unsigned>(C);
+        attr[na].val.clusterDim.y = 1;
+        attr[na].val.clusterDim.z = 1;
+        ++na;
+    }
     cfg.attrs = attr;
-    cfg.numAttrs = (flags & ATX_FLAG_PDL) ? 1 : 0;
-    cfg.gridDim = dim3(static_cast<unsigned>(T + zb));
+    cfg.numAttrs = na;
+    zb = (zb + C - 1) / C;   // zeroing CTAs come in whole clusters too
+    cfg.gridDim = dim3(static_cast<unsigned>((T + zb) * C));
     cfg.blockDim = dim3(kArThreads);
     cfg.stream = reinterpret_cast<cudaStream_t>(stream);
     ATX_CUDA(cudaLaunchKernelEx(&cfg, allreduce_add_rmsnorm_kernel, a, x, static_cast<float*>(clear_buf), clear_rows,
                                 state, rank, world, rows, reinterpret_cast<const uint2*>(w),
-                                reinterpret_cast<uint2*>(out), T, H, eps, reinterpret_cast<uint4*>(zero_ptr), zv));
+                                reinterpret_cast<uint2*>(out), T, H, eps, reinterpret_cast<uint4*>(zero_ptr), zv, C));
     return ATX_OK;
 }
 

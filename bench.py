@@ -424,6 +424,18 @@ def run_other_workload(args, rank, world, local):
         wall = max_over_ranks(dist, [time.perf_counter() - t0], "cuda")[0]
         dec = [(a.elapsed_time(b), ctx) for (a, b, nd, npf, ctx) in evs if npf == 0 and nd == B]
         ms = sum(d[0] for d in dec) / len(dec)
+        # optional A/B inside the same process (an 8-GPU box is expensive to bring up twice): decode step time
+        # with the post-all-reduce GEMMs prefetching `kb` weight slices into L2 while they wait
+        ab = {}
+        for kb in [int(v) for v in args.tp_prefetch_ab.split(",") if v.strip()]:
+            r.tp_l2_prefetch_kb = kb
+            r.close()                      # drop the captured graphs: they bake the flag in
+            one(2000 + kb)
+            _, ev2 = one(3000 + kb)
+            d2 = [a.elapsed_time(b) for (a, b, nd, npf, ctx) in ev2 if npf == 0 and nd == B]
+            ab[str(kb)] = round(max_over_ranks(dist, [sum(d2) / len(d2)], "cuda")[0], 3)
+        if ab:
+            out["tp_l2_prefetch_ab_decode_step_ms"] = ab
         byts = (mcfg.weight_bytes_per_decode_step() + mcfg.kv_bytes_per_token() * (sum(d[1] for d in dec) / len(dec))) / world
         out.update({"metric": "Llama-3.1-70B tensor-parallel decode tokens/s + p50 TTFT under agent fan-out",
                     "value": round(args.steps * B * O / wall, 1), "ms_per_step": round(1e3 * wall / args.steps, 1),
@@ -463,6 +475,8 @@ def main() -> None:
     ap.add_argument("--long-out", type=int, default=128)
     ap.add_argument("--tp-out", type=int, default=256)
     ap.add_argument("--layers", type=int, default=None, help="tp70b only: reduce depth for smoke runs")
+    ap.add_argument("--tp-prefetch-ab", default="", help="tp70b only: comma-separated ATX_TP_L2_PREFETCH_KB values "
+                                                         "to time after the main measurement")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
