@@ -73,17 +73,23 @@ class ModelRunner:
         dev = self.dev
         T, S = self.Tmax, max(self.Smax, 16)
         self.h = torch.zeros(T, H, dtype=f32, device=dev)
-        self.xn = torch.zeros(T, H, dtype=bf, device=dev)
         self.qkv = torch.zeros(T, qkv_size, dtype=f32, device=dev)
         self.q = torch.zeros(T, q_size, dtype=bf, device=dev)
         self.attn = torch.zeros(T, q_size, dtype=bf, device=dev)
         self.act = torch.zeros(T, I, dtype=bf, device=dev)
         self.part = torch.zeros(T, H, dtype=f32, device=dev) if tp > 1 else None  # partial o/down sums (TP)
         self.allreduce_calls = 0
-        self.fused_ar = False
-        if tp > 1 and os.environ.get("ATX_TP_ALLREDUCE", "fused") == "fused":
-            self._setup_fused_allreduce(T, H)
-        self.xl = torch.zeros(S, H, dtype=bf, device=dev)
+        self.fused_ar = False      # all-reduce + add + norm in our own kernel over peer memory
+        self.sharded_ar = False    # ... in its two-shot form (reduce-scatter by row, all-gather of the bf16 rows)
+        self.xn = self.xl = None
+        ar_mode = os.environ.get("ATX_TP_ALLREDUCE", "sharded" if tp > 2 else "fused")
+        if ar_mode not in ("fused", "sharded", "nccl"):
+            raise ValueError(f"ATX_TP_ALLREDUCE={ar_mode!r}: expected fused | sharded | nccl")
+        if tp > 1 and ar_mode != "nccl":
+            self._setup_fused_allreduce(T, H, S if ar_mode == "sharded" else 0)
+        if self.xn is None:   # (the two-shot kernel needs them in peer-mapped memory: allocated above)
+            self.xn = torch.zeros(T, H, dtype=bf, device=dev)
+            self.xl = torch.zeros(S, H, dtype=bf, device=dev)
         self.logits = torch.zeros(S, V, dtype=f32, device=dev)
         self.out_ids = torch.zeros(S, dtype=i32, device=dev)
         self.out_host = [torch.zeros(S, dtype=i32).pin_memory() for _ in range(2)]  # ping-pong: one step may be in flight
@@ -283,9 +289,11 @@ class ModelRunner:
     # rows up to which a step uses the fused one-shot all-reduce (beyond: NCCL's bandwidth-optimal ring)
     FUSED_AR_MAX_T = 256
 
-    def _setup_fused_allreduce(self, T: int, H: int) -> None:
+    def _setup_fused_allreduce(self, T: int, H: int, S_sharded: int = 0) -> None:
         """Symmetric (peer-mapped) ping-pong partial buffers + flag arrays for atx_allreduce_add_rmsnorm.
-        torch's symmetric-memory allocator is used only to obtain peer-mapped memory; the kernel is ours."""
+        torch's symmetric-memory allocator is used only to obtain peer-mapped memory; the kernel is ours.
+        S_sharded > 0 selects the two-shot kernel: the activation buffers xn [T, H] and xl [S, H] then live in
+        one more symmetric allocation, because every rank writes its rows into every rank's copy."""
         import torch.distributed as dist
         import torch.distributed._symmetric_memory as symm
 
@@ -298,6 +306,11 @@ class ModelRunner:
             self.sym_flags = symm.empty((64,), dtype=torch.int32, device=self.dev)
             self.sym_flags.zero_()
             hf = symm.rendezvous(self.sym_flags, group)
+            hx = None
+            if S_sharded:
+                self.sym_x = symm.empty((T + S_sharded, H), dtype=torch.bfloat16, device=self.dev)
+                self.sym_x.zero_()
+                hx = symm.rendezvous(self.sym_x, group)
         except Exception as exc:  # no peer mapping on this box: keep the NCCL path, loudly
             print(f"[atx] symmetric memory unavailable ({exc!r}); tensor-parallel all-reduce stays on NCCL", flush=True)
             return
@@ -306,7 +319,12 @@ class ModelRunner:
         self._ar_parts = [(vp * self.tp)(*[int(p) + b * stride for p in hp.buffer_ptrs]) for b in (0, 1)]
         self._ar_flags = (vp * self.tp)(*[int(p) for p in hf.buffer_ptrs])
         self._ar_state = torch.zeros(2, dtype=torch.int32, device=self.dev)
-        self._ar_handles = (hp, hf)
+        self._ar_handles = (hp, hf, hx)
+        if hx is not None:
+            self.xn, self.xl = self.sym_x[:T], self.sym_x[T:]
+            self._ar_x_base = [int(p) for p in hx.buffer_ptrs]
+            self._ar_out_ptrs = {}     # byte offset into sym_x -> array of the peers' pointers
+            self.sharded_ar = True
         torch.cuda.synchronize(self.dev)
         dist.barrier(group=group)
         self.fused_ar = True
@@ -316,6 +334,18 @@ class ModelRunner:
         """all-reduce(part[buf]) + residual add + RMSNorm; hands the other buffer back zeroed."""
         m = self.m
         other = self.sym_part[1 - buf].data_ptr()
+        if self.sharded_ar:
+            off = out_ptr - self.sym_x.data_ptr()
+            outs = self._ar_out_ptrs.get(off)
+            if outs is None:
+                assert 0 <= off < self.sym_x.numel() * 2, "two-shot all-reduce output must live in the symmetric buffer"
+                outs = self._ar_out_ptrs[off] = (C.c_void_p * self.tp)(*[b + off for b in self._ar_x_base])
+            self._ck(self.lib.atx_reduce_scatter_rmsnorm_all_gather(
+                self.h.data_ptr(), self._ar_parts[buf], self._ar_flags, outs, other, T, self._ar_state.data_ptr(),
+                self.tp_rank, self.tp, rows_ptr, w_ptr, n_rows, m.hidden_size, m.rms_norm_eps, zero_ptr, zero_bytes,
+                self.flags, st))
+            self.allreduce_calls += 1
+            return
         self._ck(self.lib.atx_allreduce_add_rmsnorm(
             self.h.data_ptr(), self._ar_parts[buf], self._ar_flags, other, T, self._ar_state.data_ptr(), self.tp_rank,
             self.tp, rows_ptr, w_ptr, out_ptr, n_rows, m.hidden_size, m.rms_norm_eps, zero_ptr, zero_bytes, self.flags,

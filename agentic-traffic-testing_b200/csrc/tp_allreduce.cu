@@ -164,6 +164,145 @@ allreduce_add_rmsnorm_kernel(ArArgs a, float* __restrict__ x, float* __restrict_
     }
 }
 
+// ---- two-shot variant: reduce-scatter by token row, RMSNorm on the owner, all-gather of the bf16 result ----
+// One-shot makes every rank pull the whole [T, H] fp32 message from every peer ((world-1) x T x H x 4 bytes
+// in, 7 MiB at 32 tokens of a 70B model on 8 GPUs). Here rank r owns the token rows t = r (mod world): it pulls
+// only those rows (1/world of the message), keeps the fp32 residual of ITS rows, and pushes the normalised
+// bf16 rows straight into every rank's activation buffer (the next GEMM's TMA operand) with peer stores:
+// (world-1)/world x T x H x (4 + 2) bytes per rank, 8x less NVLink traffic at world 8. A second cross-GPU
+// barrier, run by the last CTA out, holds the grid open until every peer's rows have landed here, so the
+// consumer needs nothing but stream order. The residual rows a rank does not own go stale and are never read.
+struct Ar2Args {
+    const float* part[kArMaxRanks];
+    int* flags[kArMaxRanks];          // int[2 * world]: [0, world) barrier 1, [world, 2 world) barrier 2
+    uint2* out[kArMaxRanks];          // every rank's activation buffer (peer-mapped), bf16 [T, H]
+};
+
+__device__ __forceinline__ void st_peer_u2(uint2* p, uint2 v) {
+    asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(v.x), "r"(v.y) : "memory");
+}
+
+__global__ void __launch_bounds__(kArThreads)
+reduce_scatter_rmsnorm_all_gather_kernel(Ar2Args a, float* __restrict__ x, float* __restrict__ clear_buf,
+                                         int clear_rows, int* __restrict__ state, int rank, int world,
+                                         const int* __restrict__ rows, const uint2* __restrict__ w, int T, int H,
+                                         float eps, uint4* __restrict__ zero_ptr, long long zero_vecs, int C,
+                                         int row_clusters) {
+    __shared__ float red[kArThreads / 32];
+    __shared__ float css;
+    __shared__ int is_last;
+    pdl_launch_dependents();
+    pdl_wait();
+    const int epoch = *reinterpret_cast<volatile int*>(state) + 1;
+    const int j = blockIdx.x / C, c = blockIdx.x % C;
+    if (j >= row_clusters) {
+        const long long first = static_cast<long long>(row_clusters) * C;
+        const long long nb = gridDim.x - first;
+        for (long long i = (blockIdx.x - first) * blockDim.x + threadIdx.x; i < zero_vecs; i += nb * blockDim.x)
+            zero_ptr[i] = make_uint4(0, 0, 0, 0);
+    } else {
+        // ---- barrier 1: every rank's GEMM has finished adding into its partial buffer
+        if (blockIdx.x == 0 && threadIdx.x < world) {
+            __threadfence_system();
+            st_release_sys(a.flags[threadIdx.x] + rank, epoch);
+        }
+        if (threadIdx.x < world) {
+            const int* f = a.flags[rank] + threadIdx.x;
+            while (ld_acquire_sys(f) < epoch) {
+            }
+        }
+        __syncthreads();
+        // the output row this cluster produces (uniform over the cluster). Ownership follows the RESIDUAL
+        // row: without a gather rank r owns t = r (mod world); with one, cluster j looks at output row j and
+        // only the rank that owns residual row rows[j] (whose x is current there) produces it.
+        const int t = rows ? j : rank + j * world;
+        const int r = (t < T) ? (rows ? rows[t] : t) : 0;
+        if (t < T && (!rows || r % world == rank)) {
+            const int nv = H / 4, per = (nv + C - 1) / C;
+            const int i = c * per + threadIdx.x;
+            const bool ok = threadIdx.x < per && i < nv;
+            float4* xr = reinterpret_cast<float4*>(x + static_cast<long long>(r) * H);
+            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+            float ss = 0.f;
+            if (ok) {
+                float4 q[kArMaxRanks];
+#pragma unroll
+                for (int p = 0; p < kArMaxRanks; ++p)
+                    if (p < world) q[p] = ld_peer_f4(a.part[p] + static_cast<long long>(r) * H + 4 * i);
+                acc = xr[i];
+#pragma unroll
+                for (int p = 0; p < kArMaxRanks; ++p) {   // fixed rank order
+                    if (p < world) {
+                        acc.x += q[p].x; acc.y += q[p].y; acc.z += q[p].z; acc.w += q[p].w;
+                    }
+                }
+                if (!rows) xr[i] = acc;
+                ss = acc.x * acc.x + acc.y * acc.y + acc.z * acc.z + acc.w * acc.w;
+            }
+            ss = warp_sum(ss);
+            if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                float tot = 0.f;
+#pragma unroll
+                for (int k = 0; k < kArThreads / 32; ++k) tot += red[k];
+                css = tot;
+            }
+            float tot;
+            if (C > 1) {
+                ar_cluster_barrier();
+                tot = 0.f;
+                for (int k = 0; k < C; ++k) tot += ar_dsmem_ld(&css, static_cast<uint32_t>(k));
+            } else {
+                __syncthreads();
+                tot = css;
+            }
+            const float rs = rsqrtf(tot / static_cast<float>(H) + eps);
+            if (ok) {
+                const uint2 wv = __ldg(w + i);
+                uint2 o;
+                o.x = pack_bf16(bf16lo(wv.x) * (acc.x * rs), bf16hi(wv.x) * (acc.y * rs));
+                o.y = pack_bf16(bf16lo(wv.y) * (acc.z * rs), bf16hi(wv.y) * (acc.w * rs));
+                const long long at = static_cast<long long>(t) * nv + i;
+#pragma unroll
+                for (int p = 0; p < kArMaxRanks; ++p)
+                    if (p < world) st_peer_u2(a.out[p] + at, o);   // all-gather by peer stores
+            }
+            if (C > 1) ar_cluster_barrier();   // peers may still be reading css
+        }
+        if (clear_buf) {
+            const long long cv = static_cast<long long>(clear_rows) * (H / 4);
+            float4* cb = reinterpret_cast<float4*>(clear_buf);
+            for (long long k = static_cast<long long>(blockIdx.x) * kArThreads + threadIdx.x; k < cv;
+                 k += static_cast<long long>(row_clusters) * C * kArThreads)
+                cb[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+    }
+    // ---- last CTA out: barrier 2 (every rank's rows have been pushed everywhere), then publish the round
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence_system();   // this CTA's peer stores (ordered before by the barrier above) become visible
+        const int prev = atomicAdd(state + 1, 1);
+        is_last = prev == static_cast<int>(gridDim.x) - 1;
+    }
+    __syncthreads();
+    if (is_last) {
+        if (threadIdx.x < world) {
+            __threadfence_system();
+            st_release_sys(a.flags[threadIdx.x] + world + rank, epoch);
+            const int* f = a.flags[rank] + world + threadIdx.x;
+            while (ld_acquire_sys(f) < epoch) {
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            state[1] = 0;
+            __threadfence();
+            *reinterpret_cast<volatile int*>(state) = epoch;
+        }
+    }
+}
+
 }  // namespace atx
 
 using namespace atx;
@@ -218,6 +357,61 @@ int atx_allreduce_add_rmsnorm(float* x, const void* const* part_ptrs, void* cons
     ATX_CUDA(cudaLaunchKernelEx(&cfg, allreduce_add_rmsnorm_kernel, a, x, static_cast<float*>(clear_buf), clear_rows,
                                 state, rank, world, rows, reinterpret_cast<const uint2*>(w),
                                 reinterpret_cast<uint2*>(out), T, H, eps, reinterpret_cast<uint4*>(zero_ptr), zv, C));
+    return ATX_OK;
+}
+
+int atx_reduce_scatter_rmsnorm_all_gather(float* x, const void* const* part_ptrs, void* const* flag_ptrs,
+                                          void* const* out_ptrs, void* clear_buf, int clear_rows, int* state, int rank,
+                                          int world, const int* rows, const void* w, int T, int H, float eps,
+                                          void* zero_ptr, long long zero_bytes, int flags, atx_stream_t stream) {
+    ATX_REQUIRE(x && part_ptrs && flag_ptrs && out_ptrs && state && w,
+                "atx_reduce_scatter_rmsnorm_all_gather: null pointer");
+    ATX_REQUIRE(world >= 2 && world <= kArMaxRanks && rank >= 0 && rank < world,
+                "atx_reduce_scatter_rmsnorm_all_gather: world=%d (2..%d), rank=%d", world, kArMaxRanks, rank);
+    ATX_REQUIRE(T > 0 && H > 0 && H % 4 == 0 && H <= kArThreads * kArMaxCluster * 4,
+                "atx_reduce_scatter_rmsnorm_all_gather: bad shape T=%d H=%d (H %% 4 == 0, H <= %d)", T, H,
+                kArThreads * kArMaxCluster * 4);
+    ATX_REQUIRE(zero_bytes >= 0 && zero_bytes % 16 == 0 && (zero_bytes == 0 || zero_ptr),
+                "atx_reduce_scatter_rmsnorm_all_gather: zero_bytes=%lld must be a non-negative multiple of 16 with a "
+                "buffer", zero_bytes);
+    Ar2Args a = {};
+    for (int p = 0; p < world; ++p) {
+        ATX_REQUIRE(part_ptrs[p] && flag_ptrs[p] && out_ptrs[p],
+                    "atx_reduce_scatter_rmsnorm_all_gather: null peer pointer for rank %d", p);
+        a.part[p] = static_cast<const float*>(part_ptrs[p]);
+        a.flags[p] = static_cast<int*>(flag_ptrs[p]);
+        a.out[p] = static_cast<uint2*>(out_ptrs[p]);
+    }
+    const long long zv = zero_bytes / 16;
+    long long zb = (zv + kArThreads * 8 - 1) / (kArThreads * 8);
+    if (zb > 1024) zb = 1024;
+    int C = 1;
+    while (C * kArThreads * 4 < H) C *= 2;
+    const int row_clusters = rows ? T : (T + world - 1) / world;   // rows t = rank, rank + world, ... (or all, filtered)
+    cudaLaunchConfig_t cfg = {};
+    cudaLaunchAttribute attr[2];
+    int na = 0;
+    if (flags & ATX_FLAG_PDL) {
+        attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[na].val.programmaticStreamSerializationAllowed = 1;
+        ++na;
+    }
+    if (C > 1) {
+        attr[na].id = cudaLaunchAttributeClusterDimension;
+        attr[na].val.clusterDim.x = static_cast<unsigned>(C);
+        attr[na].val.clusterDim.y = 1;
+        attr[na].val.clusterDim.z = 1;
+        ++na;
+    }
+    cfg.attrs = attr;
+    cfg.numAttrs = na;
+    zb = (zb + C - 1) / C;
+    cfg.gridDim = dim3(static_cast<unsigned>((row_clusters + zb) * C));
+    cfg.blockDim = dim3(kArThreads);
+    cfg.stream = reinterpret_cast<cudaStream_t>(stream);
+    ATX_CUDA(cudaLaunchKernelEx(&cfg, reduce_scatter_rmsnorm_all_gather_kernel, a, x, static_cast<float*>(clear_buf),
+                                clear_rows, state, rank, world, rows, reinterpret_cast<const uint2*>(w), T, H, eps,
+                                reinterpret_cast<uint4*>(zero_ptr), zv, C, row_clusters));
     return ATX_OK;
 }
 

@@ -97,6 +97,18 @@ int atx_allreduce_add_rmsnorm(float* x, const void* const* part_ptrs, void* cons
                               void* out, int T, int H, float eps, void* zero_ptr, long long zero_bytes, int flags,
                               atx_stream_t stream);
 
+/* Two-shot variant of the above for larger worlds: rank r owns the token rows t = r (mod world). It pulls
+ * only those rows of every peer's partial buffer, keeps the fp32 residual of its own rows in x (rows it does
+ * not own go stale: x must not be read whole between calls), and writes the normalised bf16 rows into EVERY
+ * rank's activation buffer through out_ptrs[p] (HOST array of `world` peer-mapped device pointers to the same
+ * [T, H] bf16 buffer on each rank). A second cross-GPU barrier inside the kernel keeps it running until
+ * every peer's rows have arrived here, so the consumer only needs stream order. flag_ptrs[p] must hold
+ * int[2 * world]. NVLink bytes per rank: (world-1)/world * T*H*6 instead of (world-1) * T*H*4. */
+int atx_reduce_scatter_rmsnorm_all_gather(float* x, const void* const* part_ptrs, void* const* flag_ptrs,
+                                          void* const* out_ptrs, void* clear_buf, int clear_rows, int* state, int rank,
+                                          int world, const int* rows, const void* w, int T, int H, float eps,
+                                          void* zero_ptr, long long zero_bytes, int flags, atx_stream_t stream);
+
 /* ---- RoPE + KV-cache write ------------------------------------------------------------------------
  * Replaces apply_rotary_pos_emb (modeling_llama.py:146-168, rotate_half layout :138-143) and
  * past_key_values.update (:267) / vLLM reshape_and_cache. qkv: [T, (Hq + 2*Hkv) * D] fp32 (GEMM

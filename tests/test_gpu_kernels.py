@@ -431,3 +431,64 @@ def test_allreduce_add_rmsnorm_one_gpu_fake_peers(cabi, T, H, world, use_rows):
         assert int(flags[0, 0]) == call + 1 and int(flags[1, 0]) == call + 1   # announced to every "peer"
         clear.fill_(3.0)
         zero.fill_(9.0)
+
+
+@pytest.mark.parametrize("T,H,world,use_rows", [(1, 512, 2, False), (5, 4096, 2, False), (32, 8192, 8, False),
+                                                (7, 6144, 4, True), (13, 8192, 8, True), (3, 16384, 2, False)])
+def test_reduce_scatter_rmsnorm_all_gather_one_gpu_fake_peers(cabi, T, H, world, use_rows):
+    """Two-shot form of the fused all-reduce on ONE GPU: the kernel is run once as every rank in turn (each with
+    its own residual copy, state and flag array; the other ranks' announcements pre-set by the host). Afterwards
+    every "rank's" activation buffer must hold ALL normalised rows (each produced by the rank owning that
+    residual row and pushed everywhere), and each residual copy must be updated exactly on its own rows."""
+    import ctypes as C
+
+    lib = cabi.load()
+    g = torch.Generator().manual_seed(T * 17 + H + world)
+    R_rows = T + 3
+    x0 = torch.randn(R_rows, H, generator=g)
+    parts = [torch.randn(R_rows, H, generator=g) * 0.5 for _ in range(world)]
+    w = _bf16(1 + 0.1 * torch.randn(H, generator=g))
+    rows = torch.tensor([(3 * i + 1) % R_rows for i in range(T)], dtype=torch.int32) if use_rows else None
+    xs = [x0.cuda() for _ in range(world)]
+    dparts = [p.cuda() for p in parts]
+    outs = [torch.full((T, H), float("nan"), dtype=torch.bfloat16, device="cuda") for _ in range(world)]
+    flags = torch.full((world, 64), 1 << 30, dtype=torch.int32, device="cuda")
+    states = [torch.zeros(2, dtype=torch.int32, device="cuda") for _ in range(world)]
+    clear = torch.full((R_rows, H), 3.0, device="cuda")
+    zero = torch.full((4096,), 9.0, device="cuda")
+    wd = w.cuda()
+    vp = C.c_void_p
+    part_ptrs = (vp * world)(*[p.data_ptr() for p in dparts])
+    flag_ptrs = (vp * world)(*[flags[r].data_ptr() for r in range(world)])
+    out_ptrs = (vp * world)(*[o.data_ptr() for o in outs])
+    rows_d = rows.cuda() if rows is not None else None
+    st = torch.cuda.current_stream().cuda_stream
+    for rk in range(world):
+        # slots other ranks read from rank rk start below the epoch, as on a real run
+        flags[:, rk] = 0
+        flags[:, world + rk] = 0
+        rc = lib.atx_reduce_scatter_rmsnorm_all_gather(
+            xs[rk].data_ptr(), part_ptrs, flag_ptrs, out_ptrs, clear.data_ptr(), R_rows, states[rk].data_ptr(), rk, world,
+            rows_d.data_ptr() if rows_d is not None else None, wd.data_ptr(), T, H, 1e-5, zero.data_ptr(),
+            zero.numel() * 4, 0, st)
+        assert rc == 0, lib.atx_last_error().decode()
+        torch.cuda.synchronize()
+        assert torch.all(clear == 0) and torch.all(zero == 0)
+        assert int(states[rk][0]) == 1 and int(states[rk][1]) == 0
+        assert torch.all(flags[:, rk] == 1) and torch.all(flags[:, world + rk] == 1)   # both barriers announced
+        clear.fill_(3.0)
+        zero.fill_(9.0)
+    idx = rows.long() if rows is not None else torch.arange(T)
+    summed = x0[idx].clone()
+    for p in parts:
+        summed += p[idx]
+    want = R.rms_norm(summed, w.float(), 1e-5)
+    for rk in range(world):
+        got = outs[rk].float().cpu()
+        assert torch.all((got - want).abs() <= 2 ** -8 * want.abs() + 1e-6), (rk, float((got - want).abs().max()))
+        assert torch.equal(outs[rk], outs[0])
+        want_x = x0.clone()
+        if rows is None:
+            mine = [t for t in range(T) if t % world == rk]
+            want_x[mine] = summed[mine]
+        assert torch.equal(xs[rk].cpu(), want_x)
