@@ -26,7 +26,7 @@ EXPORTS = [
     "atx_gemm_plan_create", "atx_gemm_plan_destroy", "atx_gemm_run", "atx_gemm_auto_splits",
     "atx_gemm_set_l2_prefetch",
     "atx_embed_gather", "atx_rmsnorm", "atx_rope_kv_write", "atx_silu_mul", "atx_allreduce_add_rmsnorm",
-    "atx_reduce_scatter_rmsnorm_all_gather",
+    "atx_reduce_scatter_rmsnorm_all_gather", "atx_allreduce_add_rmsnorm_ll",
     "atx_paged_attn_decode_workspace_bytes", "atx_paged_attn_decode", "atx_paged_attn_prefill",
     "atx_paged_attn_decode_static", "atx_paged_attn_decode_static_capacity",
     "atx_sample",
@@ -78,6 +78,8 @@ def load() -> C.CDLL:
                                               i32, f32, vp, i64, i32, vp]
     lib.atx_reduce_scatter_rmsnorm_all_gather.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), vp, i32, vp,
                                                           i32, i32, vp, vp, i32, i32, f32, vp, i64, i32, vp]
+    lib.atx_allreduce_add_rmsnorm_ll.argtypes = [vp, vp, C.POINTER(vp), C.POINTER(vp), vp, i32, vp, i64, i32, i32, i32,
+                                                 vp, vp, i32, i32, f32, vp, i64, i32, vp]
     lib.atx_rope_kv_write.argtypes = [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp]
     lib.atx_silu_mul.argtypes = [vp, vp, i32, i32, i32, vp]
     lib.atx_paged_attn_decode_workspace_bytes.argtypes = [i32, i32, i32, i32]

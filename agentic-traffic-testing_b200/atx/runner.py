@@ -81,15 +81,18 @@ class ModelRunner:
         self.allreduce_calls = 0
         self.fused_ar = False      # all-reduce + add + norm in our own kernel over peer memory
         self.sharded_ar = False    # ... in its two-shot form (reduce-scatter by row, all-gather of the bf16 rows)
-        self.xn = self.xl = None
-        ar_mode = os.environ.get("ATX_TP_ALLREDUCE", "sharded" if tp > 2 else "fused")
-        if ar_mode not in ("fused", "sharded", "nccl"):
-            raise ValueError(f"ATX_TP_ALLREDUCE={ar_mode!r}: expected fused | sharded | nccl")
+        self.ll_ar = False         # ... in its low-latency push form for decode-sized steps (data is the flag)
+        self.xn = self.xn2 = self.xl = None
+        ar_mode = os.environ.get("ATX_TP_ALLREDUCE", "ll")
+        if ar_mode not in ("fused", "sharded", "ll", "nccl"):
+            raise ValueError(f"ATX_TP_ALLREDUCE={ar_mode!r}: expected ll | fused | sharded | nccl")
         if tp > 1 and ar_mode != "nccl":
-            self._setup_fused_allreduce(T, H, S if ar_mode == "sharded" else 0)
-        if self.xn is None:   # (the two-shot kernel needs them in peer-mapped memory: allocated above)
+            self._setup_fused_allreduce(T, H, ar_mode, S)
+        if self.xn is None:   # (the two-shot kernels need them in peer-mapped memory: allocated above)
             self.xn = torch.zeros(T, H, dtype=bf, device=dev)
             self.xl = torch.zeros(S, H, dtype=bf, device=dev)
+        if self.xn2 is None:
+            self.xn2 = self.xn    # input of gate_up; a buffer of its own only under the low-latency all-reduce
         self.logits = torch.zeros(S, V, dtype=f32, device=dev)
         self.out_ids = torch.zeros(S, dtype=i32, device=dev)
         self.out_host = [torch.zeros(S, dtype=i32).pin_memory() for _ in range(2)]  # ping-pong: one step may be in flight
@@ -132,7 +135,7 @@ class ModelRunner:
         self.plans = []
         for l in weights.layers:
             self.plans.append((_cabi.GemmPlan(l.wqkv, self.xn), _cabi.GemmPlan(l.wo, self.attn),
-                               _cabi.GemmPlan(l.wgu, self.xn), _cabi.GemmPlan(l.wdown, self.act)))
+                               _cabi.GemmPlan(l.wgu, self.xn2), _cabi.GemmPlan(l.wdown, self.act)))
         self.plan_lm = _cabi.GemmPlan(weights.lm_head, self.xl)
 
         # ---- paged KV pools, sized from what is left of the HBM budget ---------------------------
@@ -199,6 +202,12 @@ class ModelRunner:
         dp = self._dp
         h, xn, qkv, q, attn, act = (t.data_ptr() for t in (self.h, self.xn, self.qkv, self.q, self.attn, self.act))
         fused = tp > 1 and self.fused_ar and T <= self.FUSED_AR_MAX_T
+        self._ll_now = fused and self.ll_ar and T <= self.LL_AR_MAX_T
+        xn2 = self.xn2.data_ptr()
+        if self._ll_now:
+            # steps that took another path may have left plain data in the first activation buffer: re-arm it
+            # (the other one and xl are re-armed by the first all-reduce call below)
+            self._arm_a.fill_(-32768)
         # GEMMs that follow a fused all-reduce sit idle behind a cross-GPU barrier while HBM is idle too: let
         # them pull their weight slices into L2 before they wait (per-call ATX_FLAG_L2_PREFETCH)
         fl_ar = fl | ((self.tp_l2_prefetch_kb & 0xFF) << 8) if (fused and fl) else fl
@@ -263,7 +272,7 @@ class ModelRunner:
                                               self.bs, self.MB, self.scale, fl, st))
                 n += 1
             project(p_o)
-            norm(l.ln2.data_ptr(), xn)
+            norm(l.ln2.data_ptr(), xn2)
             ck(lib.atx_gemm_run(p_gu._h, act, I, T, _cabi.GEMM_SWIGLU_BF16, 0, fl_ar, st))  # silu(g)*u in the epilogue
             n += 1
             project(p_down)
@@ -286,14 +295,18 @@ class ModelRunner:
             norm(w.norm.data_ptr(), xn)
         return n
 
-    # rows up to which a step uses the fused one-shot all-reduce (beyond: NCCL's bandwidth-optimal ring)
+    # rows up to which a step uses the fused all-reduce kernels (beyond: NCCL's bandwidth-optimal ring)
     FUSED_AR_MAX_T = 256
+    # rows up to which the low-latency push form is used: its whole grid spins on remote data and must be
+    # co-resident (rows x H/2048 CTAs <= 2 x SMs)
+    LL_AR_MAX_T = 64
 
-    def _setup_fused_allreduce(self, T: int, H: int, S_sharded: int = 0) -> None:
+    def _setup_fused_allreduce(self, T: int, H: int, mode: str = "fused", S: int = 0) -> None:
         """Symmetric (peer-mapped) ping-pong partial buffers + flag arrays for atx_allreduce_add_rmsnorm.
         torch's symmetric-memory allocator is used only to obtain peer-mapped memory; the kernel is ours.
-        S_sharded > 0 selects the two-shot kernel: the activation buffers xn [T, H] and xl [S, H] then live in
-        one more symmetric allocation, because every rank writes its rows into every rank's copy."""
+        Modes 'sharded' and 'll' (the two-shot kernels): the activation buffers xn2 / xl / xn then live in one more
+        symmetric allocation, because every rank writes its rows into every rank's copy; 'll' adds the receive
+        slots of the push protocol and arms everything with the sentinel."""
         import torch.distributed as dist
         import torch.distributed._symmetric_memory as symm
 
@@ -306,11 +319,19 @@ class ModelRunner:
             self.sym_flags = symm.empty((64,), dtype=torch.int32, device=self.dev)
             self.sym_flags.zero_()
             hf = symm.rendezvous(self.sym_flags, group)
-            hx = None
-            if S_sharded:
-                self.sym_x = symm.empty((T + S_sharded, H), dtype=torch.bfloat16, device=self.dev)
+            hx = hr = None
+            if mode in ("sharded", "ll"):
+                # activation buffers every rank writes into: A = xn2 [T, H] (gate_up input), xl [S, H] (LM-head
+                # input), B = xn [T, H] (qkv input); xl and the head of B are contiguous (one re-arm region)
+                self.sym_x = symm.empty((2 * T + S, H), dtype=torch.bfloat16, device=self.dev)
                 self.sym_x.zero_()
                 hx = symm.rendezvous(self.sym_x, group)
+            if mode == "ll":
+                cap = min(T, self.LL_AR_MAX_T)
+                self.sym_rs = symm.empty((2, self.tp, cap, H), dtype=torch.float32, device=self.dev)
+                self.sym_rs.fill_(-0.0)                                    # the sentinel: "nothing has arrived"
+                hr = symm.rendezvous(self.sym_rs, group)
+                self.sym_x.view(torch.int16).fill_(-32768)                 # bf16 -0.0
         except Exception as exc:  # no peer mapping on this box: keep the NCCL path, loudly
             print(f"[atx] symmetric memory unavailable ({exc!r}); tensor-parallel all-reduce stays on NCCL", flush=True)
             return
@@ -319,12 +340,20 @@ class ModelRunner:
         self._ar_parts = [(vp * self.tp)(*[int(p) + b * stride for p in hp.buffer_ptrs]) for b in (0, 1)]
         self._ar_flags = (vp * self.tp)(*[int(p) for p in hf.buffer_ptrs])
         self._ar_state = torch.zeros(2, dtype=torch.int32, device=self.dev)
-        self._ar_handles = (hp, hf, hx)
+        self._ar_handles = (hp, hf, hx, hr)
         if hx is not None:
-            self.xn, self.xl = self.sym_x[:T], self.sym_x[T:]
+            self.xn2, self.xl, self.xn = self.sym_x[:T], self.sym_x[T:T + S], self.sym_x[T + S:]
             self._ar_x_base = [int(p) for p in hx.buffer_ptrs]
             self._ar_out_ptrs = {}     # byte offset into sym_x -> array of the peers' pointers
             self.sharded_ar = True
+        if hr is not None:
+            cap = self.sym_rs.shape[2]
+            self._ll_cap = cap
+            self._ll_rs = [(vp * self.tp)(*[int(p) + b * self.tp * cap * H * 4 for p in hr.buffer_ptrs]) for b in (0, 1)]
+            # parity 0 writes A and re-arms xl + the head of B; parity 1 writes B (or xl) and re-arms the head of A
+            self._ll_reset = [(self.xl.data_ptr(), (S + cap) * H * 2), (self.xn2.data_ptr(), cap * H * 2)]
+            self._arm_a = self.sym_x[:cap].view(torch.int16)
+            self.ll_ar = True
         torch.cuda.synchronize(self.dev)
         dist.barrier(group=group)
         self.fused_ar = True
@@ -336,6 +365,19 @@ class ModelRunner:
         other = self.sym_part[1 - buf].data_ptr()
         if self.sharded_ar:
             off = out_ptr - self.sym_x.data_ptr()
+            if self._ll_now:
+                outs = self._ar_out_ptrs.get(off)
+                if outs is None:
+                    outs = self._ar_out_ptrs[off] = (C.c_void_p * self.tp)(*[b + off for b in self._ar_x_base])
+                in_a = off < self.xl.data_ptr() - self.sym_x.data_ptr()
+                assert in_a == (buf == 0), "activation buffer does not match the all-reduce parity"
+                reset_ptr, reset_bytes = self._ll_reset[buf]
+                self._ck(self.lib.atx_allreduce_add_rmsnorm_ll(
+                    self.h.data_ptr(), self.sym_part[buf].data_ptr(), self._ll_rs[buf], outs, other, T, reset_ptr,
+                    reset_bytes, self._ll_cap, self.tp_rank, self.tp, rows_ptr, w_ptr, n_rows, m.hidden_size,
+                    m.rms_norm_eps, zero_ptr, zero_bytes, self.flags, st))
+                self.allreduce_calls += 1
+                return
             outs = self._ar_out_ptrs.get(off)
             if outs is None:
                 assert 0 <= off < self.sym_x.numel() * 2, "two-shot all-reduce output must live in the symmetric buffer"

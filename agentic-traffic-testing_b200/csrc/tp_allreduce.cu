@@ -303,6 +303,172 @@ reduce_scatter_rmsnorm_all_gather_kernel(Ar2Args a, float* __restrict__ x, float
     }
 }
 
+// ---- low-latency variant: push + "the data is the flag" (no cross-GPU flag barrier, no pulls) -------------
+// The two kernels above pay a flag exchange (fence + store + acquire spin) and a pull round trip per call:
+// 12 us (one-shot) / 22 us (two-shot) measured back to back on B200 for a 1 MiB message, more than the GEMM
+// they follow. Here every buffer a peer writes into is kept filled with a SENTINEL bit pattern (-0.0, which a
+// sanitised payload never contains) and the receiver simply spins on the data:
+//   A  every rank reads its partial rows (local) and pushes row t to the rank that owns it, into that rank's
+//      receive slot [source][t] (fire-and-forget peer stores);
+//   B  the owner spins until all `world` slots of its rows are non-sentinel, re-arms them, adds them to its
+//      fp32 residual row in fixed source order, normalises, and pushes the bf16 row into EVERY rank's
+//      activation buffer;
+//   C  every rank spins until all T rows of its activation buffer have arrived, then the grid ends and the
+//      next GEMM (plain stream order) reads them with TMA.
+// One NVLink one-way latency per phase instead of a fence + flag + round trip. Re-arming: receive slots are
+// reset by their reader right after reading (two parities alternate); the activation buffer of the OTHER
+// parity (consumed by the GEMMs that ran before this call) is reset here via reset_ptr. A peer can only be
+// one call ahead of this rank (it needs this rank's phase-A rows to finish a call), so two parities suffice.
+constexpr uint32_t kSentinelF32 = 0x80000000u;
+constexpr uint32_t kSentinelBf16x2 = 0x80008000u;
+
+struct LlArgs {
+    float* rs[kArMaxRanks];    // rank p's receive slots of this parity (peer-mapped): fp32 [world][T_cap][H]
+    uint2* out[kArMaxRanks];   // rank p's activation buffer of this parity (peer-mapped): bf16 [>= T, H]
+};
+
+__device__ __forceinline__ void st_peer_f4(float* p, float4 v) {
+    asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+                 : "memory");
+}
+__device__ __forceinline__ uint2 ld_poll_u2(const uint2* p) {
+    uint2 v;
+    asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ float unsentinel(float v) {   // -0.0 -> +0.0, everything else unchanged
+    return __float_as_uint(v) == kSentinelF32 ? 0.f : v;
+}
+__device__ __forceinline__ uint32_t unsentinel_bf16x2(uint32_t u) {
+    if ((u & 0xffffu) == 0x8000u) u &= 0xffff0000u;
+    if ((u >> 16) == 0x8000u) u &= 0x0000ffffu;
+    return u;
+}
+__device__ __forceinline__ bool arrived(float4 q) {
+    return __float_as_uint(q.x) != kSentinelF32 && __float_as_uint(q.y) != kSentinelF32 &&
+           __float_as_uint(q.z) != kSentinelF32 && __float_as_uint(q.w) != kSentinelF32;
+}
+__device__ __forceinline__ bool arrived(uint2 u) {
+    return (u.x & 0xffffu) != 0x8000u && (u.x >> 16) != 0x8000u && (u.y & 0xffffu) != 0x8000u && (u.y >> 16) != 0x8000u;
+}
+
+__global__ void __launch_bounds__(kArThreads)
+allreduce_ll_kernel(LlArgs a, float* __restrict__ x, const float* __restrict__ part, float* __restrict__ clear_buf,
+                    int clear_rows, uint4* __restrict__ reset_ptr, long long reset_vecs, int T_cap, int rank, int world,
+                    const int* __restrict__ rows, const uint2* __restrict__ w, int T, int H, float eps,
+                    uint4* __restrict__ zero_ptr, long long zero_vecs, int C) {
+    __shared__ float red[kArThreads / 32];
+    __shared__ float css;
+    pdl_launch_dependents();
+    pdl_wait();   // this rank's GEMM has finished adding into `part`; the GEMMs reading the other parity are done
+    const int t = blockIdx.x / C, c = blockIdx.x % C;
+    const int nv = H / 4;
+    const long long gtid = static_cast<long long>(blockIdx.x) * kArThreads + threadIdx.x;
+    const long long gthreads = static_cast<long long>(gridDim.x) * kArThreads;
+    if (t < T) {
+        const int r = rows ? rows[t] : t;
+        const int owner = r % world;           // ownership follows the residual row (uniform over the cluster)
+        const int per = (nv + C - 1) / C;
+        const int i = c * per + threadIdx.x;
+        const bool ok = threadIdx.x < per && i < nv;
+        // ---- A: my partial of row t goes to its owner
+        if (ok) {
+            float4 v = *reinterpret_cast<const float4*>(part + static_cast<long long>(r) * H + 4 * i);
+            v.x = unsentinel(v.x); v.y = unsentinel(v.y); v.z = unsentinel(v.z); v.w = unsentinel(v.w);
+            st_peer_f4(a.rs[owner] + (static_cast<long long>(rank) * T_cap + t) * H + 4 * i, v);
+        }
+    }
+    // ---- housekeeping while the rows travel: re-arm the other parity's activation buffer, clear the other
+    // partial buffer, zero the split-K target of the next GEMM (all local)
+    {
+        const uint4 sent = make_uint4(kSentinelBf16x2, kSentinelBf16x2, kSentinelBf16x2, kSentinelBf16x2);
+        for (long long k = gtid; k < reset_vecs; k += gthreads) reset_ptr[k] = sent;
+        if (clear_buf) {
+            const long long cv = static_cast<long long>(clear_rows) * nv;
+            float4* cb = reinterpret_cast<float4*>(clear_buf);
+            for (long long k = gtid; k < cv; k += gthreads) cb[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        for (long long k = gtid; k < zero_vecs; k += gthreads) zero_ptr[k] = make_uint4(0, 0, 0, 0);
+    }
+    if (t >= T) return;
+    {
+        const int r = rows ? rows[t] : t;
+        const int owner = r % world;
+        const int per = (nv + C - 1) / C;
+        const int i = c * per + threadIdx.x;
+        const bool ok = threadIdx.x < per && i < nv;
+        // ---- B: the owner waits for all sources, reduces, normalises, broadcasts
+        if (owner == rank) {
+            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+            float ss = 0.f;
+            if (ok) {
+                float4* xr = reinterpret_cast<float4*>(x + static_cast<long long>(r) * H);
+                acc = xr[i];
+                float* mine = a.rs[rank] + static_cast<long long>(t) * H + 4 * i;
+                const long long src_stride = static_cast<long long>(T_cap) * H;
+                float4 q[kArMaxRanks];
+                uint32_t pending = (1u << world) - 1u;
+                while (pending) {
+#pragma unroll
+                    for (int p = 0; p < kArMaxRanks; ++p) {
+                        if (p < world && (pending >> p & 1u)) {
+                            q[p] = ld_peer_f4(mine + p * src_stride);
+                            if (arrived(q[p])) pending &= ~(1u << p);
+                        }
+                    }
+                }
+                const float4 sent = make_float4(__uint_as_float(kSentinelF32), __uint_as_float(kSentinelF32),
+                                                __uint_as_float(kSentinelF32), __uint_as_float(kSentinelF32));
+#pragma unroll
+                for (int p = 0; p < kArMaxRanks; ++p) {   // fixed source order: every run sums identically
+                    if (p < world) {
+                        *reinterpret_cast<float4*>(mine + p * src_stride) = sent;   // re-arm for the call after next
+                        acc.x += q[p].x; acc.y += q[p].y; acc.z += q[p].z; acc.w += q[p].w;
+                    }
+                }
+                if (!rows) xr[i] = acc;
+                ss = acc.x * acc.x + acc.y * acc.y + acc.z * acc.z + acc.w * acc.w;
+            }
+            ss = warp_sum(ss);
+            if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                float tot = 0.f;
+#pragma unroll
+                for (int k = 0; k < kArThreads / 32; ++k) tot += red[k];
+                css = tot;
+            }
+            float tot;
+            if (C > 1) {
+                ar_cluster_barrier();
+                tot = 0.f;
+                for (int k = 0; k < C; ++k) tot += ar_dsmem_ld(&css, static_cast<uint32_t>(k));
+            } else {
+                __syncthreads();
+                tot = css;
+            }
+            const float rs = rsqrtf(tot / static_cast<float>(H) + eps);
+            if (ok) {
+                const uint2 wv = __ldg(w + i);
+                uint2 o;
+                o.x = unsentinel_bf16x2(pack_bf16(bf16lo(wv.x) * (acc.x * rs), bf16hi(wv.x) * (acc.y * rs)));
+                o.y = unsentinel_bf16x2(pack_bf16(bf16lo(wv.y) * (acc.z * rs), bf16hi(wv.y) * (acc.w * rs)));
+                const long long at = static_cast<long long>(t) * nv + i;
+#pragma unroll
+                for (int p = 0; p < kArMaxRanks; ++p)
+                    if (p < world) st_peer_u2(a.out[p] + at, o);
+            }
+            if (C > 1) ar_cluster_barrier();   // peers may still be reading css
+        }
+        // ---- C: this rank's copy of row t has arrived (from its owner, possibly this rank itself)
+        if (ok) {
+            const uint2* mine = a.out[rank] + static_cast<long long>(t) * nv + i;
+            while (!arrived(ld_poll_u2(mine))) {
+            }
+        }
+    }
+}
+
 }  // namespace atx
 
 using namespace atx;
@@ -412,6 +578,60 @@ int atx_reduce_scatter_rmsnorm_all_gather(float* x, const void* const* part_ptrs
     ATX_CUDA(cudaLaunchKernelEx(&cfg, reduce_scatter_rmsnorm_all_gather_kernel, a, x, static_cast<float*>(clear_buf),
                                 clear_rows, state, rank, world, rows, reinterpret_cast<const uint2*>(w), T, H, eps,
                                 reinterpret_cast<uint4*>(zero_ptr), zv, C, row_clusters));
+    return ATX_OK;
+}
+
+int atx_allreduce_add_rmsnorm_ll(float* x, const float* part, void* const* rs_ptrs, void* const* out_ptrs,
+                                 void* clear_buf, int clear_rows, void* reset_ptr, long long reset_bytes, int T_cap,
+                                 int rank, int world, const int* rows, const void* w, int T, int H, float eps,
+                                 void* zero_ptr, long long zero_bytes, int flags, atx_stream_t stream) {
+    ATX_REQUIRE(x && part && rs_ptrs && out_ptrs && w, "atx_allreduce_add_rmsnorm_ll: null pointer");
+    ATX_REQUIRE(world >= 2 && world <= kArMaxRanks && rank >= 0 && rank < world,
+                "atx_allreduce_add_rmsnorm_ll: world=%d (2..%d), rank=%d", world, kArMaxRanks, rank);
+    ATX_REQUIRE(T > 0 && T <= T_cap && H > 0 && H % 4 == 0 && H <= kArThreads * kArMaxCluster * 4,
+                "atx_allreduce_add_rmsnorm_ll: bad shape T=%d (cap %d) H=%d (H %% 4 == 0, H <= %d)", T, T_cap, H,
+                kArThreads * kArMaxCluster * 4);
+    ATX_REQUIRE(zero_bytes >= 0 && zero_bytes % 16 == 0 && (zero_bytes == 0 || zero_ptr) && reset_bytes >= 0 &&
+                    reset_bytes % 16 == 0 && (reset_bytes == 0 || reset_ptr),
+                "atx_allreduce_add_rmsnorm_ll: zero_bytes=%lld / reset_bytes=%lld must be non-negative multiples of 16 "
+                "with a buffer", zero_bytes, reset_bytes);
+    int C = 1;
+    while (C * kArThreads * 4 < H) C *= 2;
+    // every CTA of the grid spins on data that other GPUs produce: the whole grid must be co-resident
+    ATX_REQUIRE(static_cast<long long>(T) * C <= 2ll * num_sms(),
+                "atx_allreduce_add_rmsnorm_ll: T=%d rows x %d CTAs exceed the co-resident grid (%d)", T, C, 2 * num_sms());
+    LlArgs a = {};
+    for (int p = 0; p < world; ++p) {
+        ATX_REQUIRE(rs_ptrs[p] && out_ptrs[p], "atx_allreduce_add_rmsnorm_ll: null peer pointer for rank %d", p);
+        a.rs[p] = static_cast<float*>(rs_ptrs[p]);
+        a.out[p] = static_cast<uint2*>(out_ptrs[p]);
+    }
+    cudaLaunchConfig_t cfg = {};
+    cudaLaunchAttribute attr[2];
+    int na = 0;
+    if (flags & ATX_FLAG_PDL) {
+        attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[na].val.programmaticStreamSerializationAllowed = 1;
+        ++na;
+    }
+    if (C > 1) {
+        attr[na].id = cudaLaunchAttributeClusterDimension;
+        attr[na].val.clusterDim.x = static_cast<unsigned>(C);
+        attr[na].val.clusterDim.y = 1;
+        attr[na].val.clusterDim.z = 1;
+        ++na;
+    }
+    cfg.attrs = attr;
+    cfg.numAttrs = na;
+    // a few extra clusters so the housekeeping stores are spread even when T is 1
+    const int extra = T * C < 32 ? (32 - T * C + C - 1) / C : 0;
+    cfg.gridDim = dim3(static_cast<unsigned>((T + extra) * C));
+    cfg.blockDim = dim3(kArThreads);
+    cfg.stream = reinterpret_cast<cudaStream_t>(stream);
+    ATX_CUDA(cudaLaunchKernelEx(&cfg, allreduce_ll_kernel, a, x, part, static_cast<float*>(clear_buf), clear_rows,
+                                reinterpret_cast<uint4*>(reset_ptr), reset_bytes / 16, T_cap, rank, world, rows,
+                                reinterpret_cast<const uint2*>(w), T, H, eps, reinterpret_cast<uint4*>(zero_ptr),
+                                zero_bytes / 16, C));
     return ATX_OK;
 }
 

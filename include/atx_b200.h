@@ -109,6 +109,24 @@ int atx_reduce_scatter_rmsnorm_all_gather(float* x, const void* const* part_ptrs
                                           int world, const int* rows, const void* w, int T, int H, float eps,
                                           void* zero_ptr, long long zero_bytes, int flags, atx_stream_t stream);
 
+/* Low-latency variant for decode-sized steps: no flag barrier and no pulls. Every buffer a peer writes into is
+ * kept filled with a sentinel bit pattern (-0.0: fp32 0x80000000, bf16 0x8000; payloads are sanitised so they
+ * never contain it) and the receiver spins on the data itself. Ownership of rows as above (t mod world).
+ *   part        this rank's partial sums [T, H] fp32 (LOCAL memory; read only)
+ *   rs_ptrs[p]  rank p's receive slots for THIS parity, fp32 [world][T_cap][H], peer-mapped, sentinel-filled once
+ *               at start-up (the kernel re-arms what it reads)
+ *   out_ptrs[p] rank p's activation buffer for THIS parity, bf16 [>= T, H], peer-mapped, sentinel in rows [0, T)
+ *               when the call starts
+ *   reset_ptr / reset_bytes  LOCAL region filled with the bf16 sentinel: the OTHER parity's activation rows,
+ *               which the GEMMs before this call have finished reading (16-byte multiple)
+ * Calls must alternate between two parities (two rs / out buffer sets), every rank making the same calls in
+ * the same order. The whole grid (T x ceil(H/2048) CTAs) spins on remote data and must be co-resident: rejected
+ * otherwise. Latency per call, 1 MiB message: see profiles/ (ar_microbench). */
+int atx_allreduce_add_rmsnorm_ll(float* x, const float* part, void* const* rs_ptrs, void* const* out_ptrs,
+                                 void* clear_buf, int clear_rows, void* reset_ptr, long long reset_bytes, int T_cap,
+                                 int rank, int world, const int* rows, const void* w, int T, int H, float eps,
+                                 void* zero_ptr, long long zero_bytes, int flags, atx_stream_t stream);
+
 /* ---- RoPE + KV-cache write ------------------------------------------------------------------------
  * Replaces apply_rotary_pos_emb (modeling_llama.py:146-168, rotate_half layout :138-143) and
  * past_key_values.update (:267) / vLLM reshape_and_cache. qkv: [T, (Hq + 2*Hkv) * D] fp32 (GEMM

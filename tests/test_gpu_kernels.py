@@ -492,3 +492,81 @@ def test_reduce_scatter_rmsnorm_all_gather_one_gpu_fake_peers(cabi, T, H, world,
             mine = [t for t in range(T) if t % world == rk]
             want_x[mine] = summed[mine]
         assert torch.equal(xs[rk].cpu(), want_x)
+
+
+@pytest.mark.parametrize("T,H,world,use_rows", [(1, 512, 2, False), (5, 4096, 2, False), (32, 8192, 8, False),
+                                                (7, 6144, 4, True), (13, 8192, 8, True), (3, 16384, 2, False)])
+def test_allreduce_ll_one_gpu_fake_peers(cabi, T, H, world, use_rows):
+    """Low-latency (push, data-is-the-flag) all-reduce + add + RMSNorm on ONE GPU, run as rank `rk` with the host
+    playing the other ranks: their partial rows are pre-written into rk's receive slots and the rows rk does not
+    own are pre-written into rk's activation buffer, so every spin in the kernel finds its data. Checks what rk
+    pushed to each owner, the rows it produced in EVERY rank's activation buffer, its residual rows, the
+    re-armed slots and the housekeeping regions, for every rk."""
+    import ctypes as C
+
+    lib = cabi.load()
+    g = torch.Generator().manual_seed(T * 29 + H + world)
+    R_rows, T_cap = T + 3, T + 2
+    x0 = torch.randn(R_rows, H, generator=g)
+    parts = [torch.randn(R_rows, H, generator=g) * 0.5 for _ in range(world)]
+    for p in parts:
+        p[0, :8] = -0.0            # a payload equal to the sentinel must be delivered as +0.0, not wait forever
+    w = _bf16(1 + 0.1 * torch.randn(H, generator=g))
+    rows = torch.tensor([(3 * i + 1) % R_rows for i in range(T)], dtype=torch.int32) if use_rows else None
+    idx = rows.long() if rows is not None else torch.arange(T)
+    summed = x0[idx].clone()
+    for p in parts:
+        summed += p[idx]
+    want = R.rms_norm(summed, w.float(), 1e-5)
+    wd = w.cuda()
+    vp = C.c_void_p
+    st = torch.cuda.current_stream().cuda_stream
+    SENT16 = -32768
+    for rk in range(world):
+        owner = [int(idx[t]) % world for t in range(T)]
+        rs = [torch.full((world, T_cap, H), -0.0, device="cuda") for _ in range(world)]      # every rank's slots
+        outs = [torch.full((T + 1, H), 0, dtype=torch.int16, device="cuda").fill_(SENT16) for _ in range(world)]
+        for t in range(T):
+            if owner[t] == rk:
+                for src in range(world):
+                    if src != rk:
+                        rs[rk][src, t] = (parts[src][idx[t]] + 0.0).cuda()   # "peers have pushed" (sanitised)
+            else:
+                outs[rk][t] = 0x3F80                                     # "the owner has broadcast" (bf16 1.0)
+        x = x0.cuda()
+        part = parts[rk].cuda()
+        clear = torch.full((R_rows, H), 3.0, device="cuda")
+        zero = torch.full((4096,), 9.0, device="cuda")
+        reset = torch.zeros(2048, dtype=torch.int16, device="cuda")
+        rc = lib.atx_allreduce_add_rmsnorm_ll(
+            x.data_ptr(), part.data_ptr(), (vp * world)(*[r.data_ptr() for r in rs]),
+            (vp * world)(*[o.data_ptr() for o in outs]), clear.data_ptr(), R_rows, reset.data_ptr(), reset.numel() * 2,
+            T_cap, rk, world, rows.cuda().data_ptr() if rows is not None else None, wd.data_ptr(), T, H, 1e-5,
+            zero.data_ptr(), zero.numel() * 4, 0, st)
+        assert rc == 0, lib.atx_last_error().decode()
+        torch.cuda.synchronize()
+        assert torch.all(clear == 0) and torch.all(zero == 0) and torch.all(reset == SENT16)
+        want_x = x0.clone()
+        for t in range(T):
+            o = owner[t]
+            if o == rk:
+                for p_ in range(world):     # produced here, delivered everywhere, bit-identical
+                    got = outs[p_][t].view(torch.bfloat16).float().cpu()
+                    assert torch.all((got - want[t]).abs() <= 2 ** -8 * want[t].abs() + 1e-6), (rk, t, p_)
+                    assert torch.equal(outs[p_][t], outs[rk][t])
+                assert torch.all(rs[rk][:, t].view(torch.int32) == -2 ** 31)      # slots re-armed
+                if rows is None:
+                    want_x[t] = summed[t]
+            else:
+                pushed = rs[o][rk, t].cpu()
+                assert torch.equal(pushed, parts[rk][idx[t]] + 0.0)               # my partial, -0.0 sanitised
+                for p_ in range(world):
+                    if p_ != rk:
+                        assert torch.all(outs[p_][t] == SENT16)                   # not mine to broadcast
+        assert torch.all(outs[rk][T] == SENT16)
+        assert torch.equal(x.cpu(), want_x)
+    with pytest.raises(cabi.AtxError, match="co-resident"):
+        cabi._check(lib.atx_allreduce_add_rmsnorm_ll(
+            x.data_ptr(), part.data_ptr(), (vp * world)(*[r.data_ptr() for r in rs]),
+            (vp * world)(*[o.data_ptr() for o in outs]), None, 0, None, 0, 4096, 0, world, None, wd.data_ptr(), 4096, H,
+            1e-5, None, 0, 0, st))

@@ -50,13 +50,14 @@ def _rank(rank, world, port, graphs, mode, q):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("mode", ["fused", "sharded", "nccl"])
+@pytest.mark.parametrize("mode", ["ll", "fused", "sharded", "nccl"])
 @pytest.mark.parametrize("graphs", [False, True])
 def test_tp2_matches_hf_golden(graphs, mode):
     """mode 'fused': all-reduce + residual add + RMSNorm in one kernel over NVLink peer memory
     (atx_allreduce_add_rmsnorm); mode 'sharded': its two-shot form, reduce-scatter by token row + norm on the
-    owner + all-gather by peer stores (atx_reduce_scatter_rmsnorm_all_gather); mode 'nccl': NCCL all-reduce +
-    fused add/norm kernel."""
+    owner + all-gather by peer stores (atx_reduce_scatter_rmsnorm_all_gather); mode 'll': the same data flow
+    pushed, with the data as the flag (atx_allreduce_add_rmsnorm_ll); mode 'nccl': NCCL all-reduce + fused
+    add/norm kernel."""
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     with socket.socket() as s:
