@@ -447,10 +447,15 @@ def run_other_workload(args, rank, world, local):
                                     "allreduces_per_step": 2 * mcfg.num_hidden_layers + 1,
                                     "allreduce_message_bytes": B * mcfg.hidden_size * 4},
                     "gpu_launches": r.kernel_launches,
+                    "tp_allreduce": ("ll: push protocol, data is the flag (atx_allreduce_add_rmsnorm_ll)" if r.ll_ar else
+                                     "sharded: flag barrier + reduce-scatter/all-gather kernel" if r.sharded_ar else
+                                     "fused: flag barrier + one-shot kernel" if r.fused_ar else "nccl"),
                     "config": {"workload": f"BASELINE configs[3]: Llama-3.1-70B ({mcfg.num_hidden_layers} layers) tensor-"
-                                           f"parallel TP={world}, NCCL all-reduce over NVLink, agent fan-out batch {B}, "
-                                           f"{P}-token prompts (768 shared), {O} greedy tokens; decode steps replayed as CUDA graphs "
-                                           "with the NCCL all-reduces captured",
+                                           f"parallel TP={world} over NVLink, agent fan-out batch {B}, {P}-token prompts "
+                                           f"(768 shared), {O} greedy tokens; the per-layer all-reduce is fused with the "
+                                           "residual add and RMSNorm in our own kernel for decode-sized steps (see "
+                                           "tp_allreduce), NCCL for prefill-sized steps and the logits; decode steps "
+                                           "replayed as CUDA graphs",
                                "parallelism": f"tp{world}"}})
     if rank == 0:
         print(json.dumps(out), flush=True)
