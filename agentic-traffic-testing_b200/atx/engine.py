@@ -151,8 +151,12 @@ class _Stream:
 class AsyncEngine:
     """Thread-backed engine with an asyncio streaming interface (one per GPU / replica)."""
 
-    def __init__(self, engine: LLMEngine):
+    def __init__(self, engine: LLMEngine, tp_group=None):
+        """tp_group (atx.tp_group.TPGroup): `engine` is rank 0 of a tensor-parallel group; every batch of
+        add/abort messages is sent to the follower ranks before it is applied here, one send per loop
+        iteration, so all ranks make the same calls in the same order."""
         self.engine = engine
+        self._tp = tp_group
         self._inbox: List = []
         self._cv = threading.Condition()
         self._streams: Dict[str, _Stream] = {}
@@ -195,7 +199,10 @@ class AsyncEngine:
             self._cv.notify()
         self._thread.join(timeout=10)
         if not self._thread.is_alive():
-            self.engine.runner.close()
+            if self._tp is not None:
+                self._tp.shutdown()
+            else:
+                self.engine.runner.close()
 
     # ---- facts the HTTP layer exports ---------------------------------------------------------------
     @property
@@ -224,7 +231,8 @@ class AsyncEngine:
     def _run(self) -> None:
         eng = self.engine
         try:
-            torch.cuda.set_device(eng.runner.dev)
+            if eng.runner.dev is not None:
+                torch.cuda.set_device(eng.runner.dev)
             while True:
                 with self._cv:
                     while not self._inbox and not eng.has_work() and not self._stop:
@@ -232,16 +240,19 @@ class AsyncEngine:
                     if self._stop:
                         return
                     inbox, self._inbox = self._inbox, []
+                if self._tp is not None:
+                    self._tp.broadcast(inbox)   # followers apply the same messages, then step iff they have work
                 for msg in inbox:
                     if msg[0] == "add":
                         _, rid, ids, params = msg
                         st = self._streams.get(rid)
-                        if st is None:
-                            continue
-                        try:
-                            st.seq = eng.add_request(rid, ids, params)
+                        try:   # a request whose client already left is added all the same (its abort follows):
+                            seq = eng.add_request(rid, ids, params)   # every rank must see the same calls
+                            if st is not None:
+                                st.seq = seq
                         except Exception as exc:  # bad request: surface to the awaiting handler
-                            self._post(st, exc)
+                            if st is not None:
+                                self._post(st, exc)
                     else:
                         eng.abort(msg[1])
                 if not eng.has_work():

@@ -106,26 +106,56 @@ class ModelWeights:
                tp_rank: int = 0) -> "ModelWeights":
         """Seeded random init generated ON the device (16 GB for 8B in well under a second). Values
         do not match the CPU-seeded oracle weights; parity tests use from_state_dict instead. With
-        tp_size > 1 only a shard-shaped set is generated (70B: 17.4 GB per rank at tp 8)."""
+        tp_size > 1 every rank draws the SAME stream (one full matrix at a time, a transient of at most
+        2 I x H fp32) and keeps its Megatron shard, so the ranks hold shards of ONE model, the model
+        `random(seed)` builds on a single GPU: replicated tensors agree and TP results can be checked
+        against the unsharded engine (70B: 17.4 GB per rank at tp 8)."""
         w = cls(cfg, device)
         w.tp_size, w.tp_rank = tp_size, tp_rank
-        g = torch.Generator(device=device).manual_seed(seed * 1000 + tp_rank)
-        H, I = cfg.hidden_size, cfg.intermediate_size // tp_size
+        n, r = tp_size, tp_rank
+        g = torch.Generator(device=device).manual_seed(seed * 1000)
+        H, I = cfg.hidden_size, cfg.intermediate_size
+        D, q_size = cfg.head_dim, cfg.q_size
+        kv_size = (cfg.qkv_size - q_size) // 2
 
-        def mat(n, k):
-            return (torch.randn(n, k, generator=g, device=device, dtype=torch.float32) * std).to(torch.bfloat16)
+        def mat(rows, k):
+            return (torch.randn(rows, k, generator=g, device=device, dtype=torch.float32) * std).to(torch.bfloat16)
 
-        def vec(n):
-            return (1.0 + 0.1 * torch.randn(n, generator=g, device=device)).to(torch.bfloat16)
+        def vec(k):
+            return (1.0 + 0.1 * torch.randn(k, generator=g, device=device)).to(torch.bfloat16)
+
+        def rshard(t, lo=0, size=None):   # row shard of the block [lo, lo + size)
+            size = t.shape[0] - lo if size is None else size
+            k = size // n
+            return t[lo + r * k: lo + (r + 1) * k]
+
+        def cshard(t):
+            k = t.shape[1] // n
+            return t[:, r * k:(r + 1) * k].contiguous()
 
         w.embed = mat(cfg.vocab_size, H)
         for _ in range(cfg.num_hidden_layers):
             l = LayerWeights()
-            l.ln1, l.wqkv, l.wo = vec(H), mat(cfg.qkv_size // tp_size, H), mat(H, cfg.q_size // tp_size)
-            l.ln2, l.wgu, l.wdown = vec(H), mat(2 * I, H), mat(H, I)
+            l.ln1 = vec(H)
+            wqkv, wo = mat(cfg.qkv_size, H), mat(H, q_size)
+            l.ln2 = vec(H)
+            wgu, wdown = mat(2 * I, H), mat(H, I)
+            if n == 1:
+                l.wqkv, l.wo, l.wgu, l.wdown = wqkv, wo, wgu, wdown
+            else:
+                l.wqkv = torch.cat([rshard(wqkv, 0, q_size), rshard(wqkv, q_size, kv_size),
+                                    rshard(wqkv, q_size + kv_size, kv_size)], dim=0).contiguous()
+                l.wo = cshard(wo)
+                l.wgu = rshard(wgu).contiguous()   # interleaved 64-row gate/up groups: a row block IS a feature block
+                l.wdown = cshard(wdown)
+                del wqkv, wo, wgu, wdown
             w.layers.append(l)
         w.norm = vec(H)
-        w.lm_head = w.embed if (cfg.tie_word_embeddings and tp_size == 1) else mat(cfg.vocab_size // tp_size, H)
+        if cfg.tie_word_embeddings:
+            w.lm_head = w.embed if n == 1 else rshard(w.embed).contiguous()
+        else:
+            head = mat(cfg.vocab_size, H)
+            w.lm_head = head if n == 1 else rshard(head).contiguous()
         w._check()
         return w
 

@@ -76,7 +76,15 @@ class B200Backend:
         )
         self._ecfg = ecfg
         self._vocab = src.config.vocab_size
-        if dp > 1:
+        tp = int(os.environ.get("LLM_TP_SIZE") or os.environ.get("LLM_TENSOR_PARALLEL_SIZE") or "1")
+        if tp > 1 and dp > 1:
+            raise ValueError("LLM_TP_SIZE and LLM_DP_SIZE cannot both be > 1")
+        if tp > 1:     # 70B-class models: one model sharded over `tp` GPUs of the box
+            from atx.tp_group import TPGroup
+
+            group = TPGroup(model, ecfg, tp)
+            self._engine = AsyncEngine(group.engine, tp_group=group)
+        elif dp > 1:
             from atx.router import ReplicaPool
 
             self._engine = ReplicaPool(model, ecfg, dp)

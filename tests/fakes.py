@@ -60,3 +60,60 @@ def fake_replica_worker(rank, model, ecfg, req, resp):
             for i in range(n):
                 toks = [1000 * rank + j for j in range(i + 1)]
                 resp.send(("out", rid, toks, i == n - 1, "length" if i == n - 1 else None, len(ids), 0))
+
+
+class _LogicRunner:
+    """Runner double for host-logic tests: 'samples' a deterministic token per (request, position)."""
+
+    dev = None
+    num_blocks = 64
+    kernel_launches = 0
+
+    def launch(self, plan, chained=False):
+        out = {}
+        for c in plan.decodes + plan.prefills:
+            if c.samples:
+                out[c.seq.uid] = (hash((c.seq.request_id, c.start + c.count)) & 0x7FFFFFFF) % 1000
+        return out
+
+    def wait(self, handle):
+        return handle or {}
+
+    def close(self):
+        pass
+
+    def kv_cache_info(self):
+        return self.num_blocks, 16
+
+
+def make_logic_engine(max_num_seqs=4, max_num_batched_tokens=48, max_model_len=256, num_blocks=64,
+                      async_scheduling=True):
+    """An LLMEngine with the REAL scheduler, block allocator and step()/chaining logic over a runner double:
+    records the plan of every step in `.trace` so two engines can be compared call for call (CPU only)."""
+    from atx.config import EngineConfig, model_config_by_name
+    from atx.engine import LLMEngine
+    from atx.kv_cache import BlockAllocator
+    from atx.scheduler import Scheduler
+
+    eng = LLMEngine.__new__(LLMEngine)
+    eng.mcfg = model_config_by_name("tiny")
+    eng.ecfg = EngineConfig(max_model_len=max_model_len, max_num_seqs=max_num_seqs,
+                            max_num_batched_tokens=max_num_batched_tokens, num_gpu_blocks=num_blocks,
+                            async_scheduling=async_scheduling)
+    eng.runner = _LogicRunner()
+    eng.runner.num_blocks = num_blocks
+    eng.allocator = BlockAllocator(num_blocks, 16, True)
+    eng.scheduler = Scheduler(eng.allocator, max_num_seqs, max_num_batched_tokens, max_model_len, eng.mcfg.eos_token_ids)
+    eng.steps = 0
+    eng.batch_size_observer = None
+    eng._inflight = None
+    eng.trace = []
+    real_launch = eng.runner.launch
+
+    def launch(plan, chained=False):
+        eng.trace.append((chained, tuple((c.seq.request_id, c.start, c.count, c.samples) for c in plan.decodes),
+                          tuple((c.seq.request_id, c.start, c.count, c.samples) for c in plan.prefills),
+                          tuple(tuple(c.seq.blocks.table) for c in plan.decodes + plan.prefills)))
+        return real_launch(plan, chained)
+    eng.runner.launch = launch
+    return eng

@@ -1,0 +1,71 @@
+"""Host logic of the tensor-parallel server group (atx/tp_group.py) on CPU: the follower ranks, fed only the
+request stream rank 0 broadcasts, must make exactly the calls rank 0 makes — same admissions, same chunking,
+same block tables, same chained (async-scheduled) steps — including requests rejected at admission and clients
+that leave early. Real scheduler, allocator and LLMEngine.step(); the runner is a double (tests/fakes.py)."""
+import asyncio
+
+import pytest
+
+from atx.engine import AsyncEngine
+from atx.scheduler import SamplingParams
+from atx.tp_group import apply_messages
+from tests.fakes import make_logic_engine
+
+
+class _InProcessGroup:
+    """TPGroup double: the 'follower' is a second logic engine in this process, driven synchronously by exactly
+    what TPGroup.broadcast would put on the pipe (atx/tp_group.py:_follower)."""
+
+    def __init__(self, follower):
+        self.follower = follower
+        self.sent = []
+
+    def broadcast(self, msgs):
+        item = ("step", list(msgs))
+        self.sent.append(item)
+        apply_messages(self.follower, item[1])
+        if self.follower.has_work():
+            self.follower.step()
+
+    def shutdown(self):
+        pass
+
+
+@pytest.mark.parametrize("async_sched", [True, False])
+def test_followers_mirror_rank0_call_for_call(async_sched):
+    lead, follow = make_logic_engine(async_scheduling=async_sched), make_logic_engine(async_scheduling=async_sched)
+    group = _InProcessGroup(follow)
+    ae = AsyncEngine(lead, tp_group=group)
+    shared = list(range(100, 140))
+
+    async def one(i, n_new, leave_after=None):
+        got = []
+        params = SamplingParams(temperature=0.0, max_tokens=n_new, ignore_eos=True, stream=True)
+        async for out in ae.generate(shared + [i] * (5 + 3 * i), params, f"r{i}"):
+            got = out.token_ids
+            if leave_after is not None and len(got) >= leave_after:
+                break                      # client goes away: rank 0 queues an abort, followers must see it too
+        return got
+
+    async def bad():
+        with pytest.raises(ValueError):
+            async for _ in ae.generate([5] * 300, SamplingParams(max_tokens=4), "too-long"):   # > max_model_len
+                pass
+
+    async def main():
+        first = await asyncio.gather(one(0, 9), one(1, 4), one(2, 12, leave_after=3), bad(), one(3, 6), one(4, 7))
+        second = await asyncio.gather(one(5, 5), one(6, 3))
+        return first, second
+
+    try:
+        first, second = asyncio.run(main())
+    finally:
+        ae.shutdown()
+    assert [len(x) for x in (first[0], first[1], first[4], first[5])] == [9, 4, 6, 7]
+    assert [len(x) for x in second] == [5, 3]
+    assert lead.trace, "rank 0 ran no steps"
+    assert follow.trace == lead.trace                      # every step: same chunks, same block tables, same chaining
+    assert any(t[0] for t in lead.trace) == async_sched    # chained steps are mirrored too
+    assert any(m[0] == "abort" for item in group.sent for m in item[1])
+    assert not follow.has_work() and not lead.has_work()
+    assert follow.allocator.num_used == lead.allocator.num_used
