@@ -382,6 +382,10 @@ def build_arg_parser() -> argparse.ArgumentParser:
     ap.add_argument("--max-num-seqs", type=int, default=None, help="Max sequences per iteration.")
     ap.add_argument("--max-num-batched-tokens", type=int, default=None, help="Max batched tokens per iteration.")
     ap.add_argument("--gpu-memory-utilization", type=float, default=None, help="Target HBM fraction (0-1).")
+    ap.add_argument("--tensor-parallel-size", type=int, default=None,
+                    help="Additive: shard the model over this many GPUs of the box (env LLM_TP_SIZE).")
+    ap.add_argument("--data-parallel-size", type=int, default=None,
+                    help="Additive: this many full replicas, one per GPU (env LLM_DP_SIZE).")
     return ap
 
 
@@ -389,6 +393,10 @@ def main(argv: Optional[List[str]] = None) -> None:
     args = build_arg_parser().parse_args(argv)
     # CLI wins over env (reference :1101-1104)
     dtype = args.dtype or LLM_DTYPE
+    if args.tensor_parallel_size:
+        os.environ["LLM_TP_SIZE"] = str(args.tensor_parallel_size)
+    if args.data_parallel_size:
+        os.environ["LLM_DP_SIZE"] = str(args.data_parallel_size)
     max_num_seqs = args.max_num_seqs or _env_number(LLM_MAX_NUM_SEQS, int)
     max_batched = args.max_num_batched_tokens or _env_number(LLM_MAX_NUM_BATCHED_TOKENS, int)
     gpu_util = args.gpu_memory_utilization or _env_number(LLM_GPU_MEMORY_UTILIZATION, float)
