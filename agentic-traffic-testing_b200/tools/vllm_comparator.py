@@ -59,7 +59,7 @@ def main() -> int:
         (Path(d) / "config.json").write_text(json.dumps(LLAMA_8B))
         llm = LLM(model=d, load_format="dummy", skip_tokenizer_init=True, dtype="bfloat16", max_model_len=4096,
                   max_num_seqs=12, max_num_batched_tokens=8192, gpu_memory_utilization=0.90,
-                  enable_prefix_caching=True, enforce_eager=a.eager, seed=0)
+                  enable_prefix_caching=True, enforce_eager=a.eager, seed=0, disable_log_stats=False)
         sp = SamplingParams(temperature=0.0, max_tokens=OUT, ignore_eos=True, detokenize=False)
         times, ttfts = [], []
         for step in range(-a.warmup, a.steps):
@@ -76,6 +76,16 @@ def main() -> int:
                     lat = getattr(m, "first_token_latency", 0.0) if m is not None else 0.0
                     if lat:
                         ttfts.append(lat)
+        # time to first token: per-request engine stats when vLLM exposes them, and in any case the wall time of
+        # a fresh burst cut at ONE token (= the time until the LAST of the 6 requests has its first token)
+        sp1 = SamplingParams(temperature=0.0, max_tokens=1, ignore_eos=True, detokenize=False)
+        first = []
+        for k in range(5):
+            prompts = [{"prompt_token_ids": p} for p in burst_prompts(500 + k)]
+            t0 = time.perf_counter()
+            llm.generate(prompts, sp1, use_tqdm=False)
+            first.append(time.perf_counter() - t0)
+        out["burst_first_token_ms_p50"] = round(1e3 * sorted(first)[len(first) // 2], 2)
         total = sum(times)
         out.update({"value": round(BATCH * OUT * len(times) / total, 1), "unit": "tokens/s", "steps": a.steps,
                     "warmup": a.warmup, "ms_per_step": round(1e3 * total / len(times), 2), "timing": "wall clock",

@@ -59,3 +59,40 @@ def test_interleave_layout():
     w = interleave_gate_up(gate, up)
     assert torch.equal(w[:64], gate[:64]) and torch.equal(w[64:128], up[:64])
     assert torch.equal(w[128:192], gate[64:]) and torch.equal(w[192:], up[64:])
+
+
+def test_random_init_tp_shards_are_slices_of_the_single_gpu_model():
+    """ModelWeights.random(tp_size=n) must give every rank the Megatron shard of the SAME model that
+    random(tp_size=1) builds (bytes equal), replicated tensors identical on all ranks, so that tensor-parallel
+    results can be checked against the unsharded engine and the ranks agree on embeddings and norms."""
+    import torch
+
+    from atx.config import model_config_by_name
+    from atx.weights import ModelWeights
+
+    for name in ("tiny", "tiny128"):
+        cfg = model_config_by_name(name)
+        dev = torch.device("cpu")
+        full = ModelWeights.random(cfg, 7, dev)
+        n = 2 if cfg.num_key_value_heads % 2 == 0 else 1
+        if name == "tiny128":
+            n = 1 if cfg.num_key_value_heads < 2 else 2
+        if n == 1:
+            continue
+        D, Hq, Hkv, I = cfg.head_dim, cfg.num_attention_heads, cfg.num_key_value_heads, cfg.intermediate_size
+        q_size, kv = Hq * D, Hkv * D
+        for r in range(n):
+            w = ModelWeights.random(cfg, 7, dev, tp_size=n, tp_rank=r)
+            assert torch.equal(w.embed, full.embed) and torch.equal(w.norm, full.norm)
+            for lf, ls in zip(full.layers, w.layers):
+                assert torch.equal(ls.ln1, lf.ln1) and torch.equal(ls.ln2, lf.ln2)
+                qs, ks = q_size // n, kv // n
+                want_qkv = torch.cat([lf.wqkv[r * qs:(r + 1) * qs], lf.wqkv[q_size + r * ks: q_size + (r + 1) * ks],
+                                      lf.wqkv[q_size + kv + r * ks: q_size + kv + (r + 1) * ks]])
+                assert torch.equal(ls.wqkv, want_qkv)
+                assert torch.equal(ls.wo, lf.wo[:, r * qs:(r + 1) * qs])
+                rows = 2 * I // n
+                assert torch.equal(ls.wgu, lf.wgu[r * rows:(r + 1) * rows])
+                assert torch.equal(ls.wdown, lf.wdown[:, r * (I // n):(r + 1) * (I // n)])
+            V = cfg.vocab_size // n
+            assert torch.equal(w.lm_head, full.lm_head[r * V:(r + 1) * V])
