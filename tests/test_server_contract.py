@@ -229,3 +229,25 @@ def test_cli_and_env_precedence(monkeypatch):
     with pytest.raises(SystemExit) as e:
         S.main(["--tp-size", "8"])  # unknown flags stay an argparse error (exit 2), as in the reference
     assert e.value.code == 2
+
+
+def test_cli_parallelism_flags_are_additive_and_set_the_env(monkeypatch):
+    """--tensor-parallel-size / --data-parallel-size do not exist in the reference CLI (llm/serve_llm.py:1049-1104
+    is single-GPU); here they are additive switches that only select how B200Backend builds its engine."""
+    import os
+
+    from llm import serve_llm as S
+
+    async def fake_run(*a):
+        pass
+    monkeypatch.setattr(S, "run_async_server", fake_run)
+    monkeypatch.delenv("LLM_TP_SIZE", raising=False)
+    monkeypatch.delenv("LLM_DP_SIZE", raising=False)
+    S.main(["--model", "random:tiny"])
+    assert "LLM_TP_SIZE" not in os.environ and "LLM_DP_SIZE" not in os.environ
+    S.main(["--model", "random:70b:0", "--tensor-parallel-size", "8"])
+    assert os.environ["LLM_TP_SIZE"] == "8" and "LLM_DP_SIZE" not in os.environ
+    monkeypatch.delenv("LLM_TP_SIZE", raising=False)
+    S.main(["--model", "random:8b:0", "--data-parallel-size", "4"])
+    assert os.environ["LLM_DP_SIZE"] == "4"
+    monkeypatch.delenv("LLM_DP_SIZE", raising=False)
