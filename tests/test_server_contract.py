@@ -251,3 +251,12 @@ def test_cli_parallelism_flags_are_additive_and_set_the_env(monkeypatch):
     S.main(["--model", "random:8b:0", "--data-parallel-size", "4"])
     assert os.environ["LLM_DP_SIZE"] == "4"
     monkeypatch.delenv("LLM_DP_SIZE", raising=False)
+
+
+def test_backend_rejects_tp_and_dp_together(monkeypatch):
+    from llm.backend import B200Backend
+
+    monkeypatch.setenv("LLM_TP_SIZE", "2")
+    monkeypatch.setenv("LLM_DP_SIZE", "2")
+    with pytest.raises(ValueError, match="cannot both"):
+        B200Backend("random:tiny", 256, None, 4, 64, 0.5)
