@@ -17,11 +17,28 @@ sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
 from atx import _cabi  # noqa: E402
 
 
-def time_ms(fn, iters=20, warmup=3):
+def time_ms(fn, iters=20, warmup=3, graph=True):
+    """Average device time of fn(). The `iters` calls are captured into ONE CUDA graph and replayed, so kernels
+    shorter than a ctypes call (~10 us of host time) are timed at the device's pace, not the interpreter's."""
     for _ in range(warmup):
         fn()
     torch.cuda.synchronize()
     s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if graph:
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.stream(side):
+            with torch.cuda.graph(g, stream=side):
+                for _ in range(iters):
+                    fn()
+            g.replay()   # warm the instantiated graph
+            side.synchronize()
+            s.record(side)
+            g.replay()
+            e.record(side)
+            side.synchronize()
+        return s.elapsed_time(e) / iters
     s.record()
     for _ in range(iters):
         fn()
