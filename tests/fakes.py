@@ -2,6 +2,7 @@
 from __future__ import annotations
 
 import asyncio
+import zlib
 from typing import List
 
 from atx.engine import RequestOutput
@@ -73,7 +74,7 @@ class _LogicRunner:
         out = {}
         for c in plan.decodes + plan.prefills:
             if c.samples:
-                out[c.seq.uid] = (hash((c.seq.request_id, c.start + c.count)) & 0x7FFFFFFF) % 1000
+                out[c.seq.uid] = zlib.crc32(f"{c.seq.request_id}:{c.start + c.count}".encode()) % 1000
         return out
 
     def wait(self, handle):
