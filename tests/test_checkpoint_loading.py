@@ -1,0 +1,83 @@
+"""Loading a real HF-format checkpoint directory (what `--model /models/Llama-3.1-8B-Instruct` points at): the
+directory is written by transformers' own `save_pretrained` (config.json + model.safetensors; tied heads are
+NOT stored, as in the public 1B / 3B checkpoints), read back by atx.config.resolve_model +
+ModelWeights.from_hf_dir, and must give the layout the kernels stream: fused q/k/v, gate/up interleaved in
+64-row groups, bf16 bytes equal to the checkpoint's, Megatron shards under tensor parallelism. CPU only."""
+import json
+
+import pytest
+import torch
+
+from atx.config import resolve_model
+from atx.weights import ModelWeights, interleave_gate_up
+
+
+def _write_checkpoint(tmp_path, tie: bool):
+    from transformers import LlamaConfig, LlamaForCausalLM
+
+    cfg = LlamaConfig(vocab_size=512, hidden_size=256, intermediate_size=512, num_hidden_layers=2,
+                      num_attention_heads=4, num_key_value_heads=2, head_dim=64, max_position_embeddings=4096,
+                      rms_norm_eps=1e-5, rope_theta=500000.0, tie_word_embeddings=tie,
+                      rope_scaling={"rope_type": "llama3", "factor": 8.0, "low_freq_factor": 1.0,
+                                    "high_freq_factor": 4.0, "original_max_position_embeddings": 8192},
+                      bos_token_id=1, eos_token_id=[2, 3], torch_dtype="bfloat16")
+    torch.manual_seed(4)
+    model = LlamaForCausalLM(cfg).to(torch.bfloat16)
+    d = tmp_path / ("tied" if tie else "untied")
+    model.save_pretrained(d, safe_serialization=True)
+    return d, model
+
+
+@pytest.mark.parametrize("tie", [False, True])
+def test_hf_checkpoint_directory_round_trip(tmp_path, tie):
+    d, model = _write_checkpoint(tmp_path, tie)
+    assert list(d.glob("*.safetensors")) and (d / "config.json").exists()
+    src = resolve_model(str(d))
+    m = src.config
+    raw = json.loads((d / "config.json").read_text())
+    assert src.path == d and src.random_seed is None
+    assert (m.vocab_size, m.hidden_size, m.intermediate_size, m.num_hidden_layers) == (512, 256, 512, 2)
+    assert (m.num_attention_heads, m.num_key_value_heads, m.head_dim) == (4, 2, 64)
+    assert m.tie_word_embeddings == tie and m.rms_norm_eps == raw["rms_norm_eps"]
+    assert set(m.eos_token_ids) == {2, 3}
+    sd = model.state_dict()
+    dev = torch.device("cpu")
+    w = ModelWeights.from_hf_dir(m, d, dev)
+    assert torch.equal(w.embed, sd["model.embed_tokens.weight"])
+    head = sd["model.embed_tokens.weight"] if tie else sd["lm_head.weight"]
+    assert torch.equal(w.lm_head, head) and (w.lm_head is w.embed) == tie
+    for i, l in enumerate(w.layers):
+        p = f"model.layers.{i}."
+        assert torch.equal(l.wqkv, torch.cat([sd[p + "self_attn.q_proj.weight"], sd[p + "self_attn.k_proj.weight"],
+                                              sd[p + "self_attn.v_proj.weight"]]))
+        assert torch.equal(l.wo, sd[p + "self_attn.o_proj.weight"])
+        assert torch.equal(l.wgu, interleave_gate_up(sd[p + "mlp.gate_proj.weight"], sd[p + "mlp.up_proj.weight"]))
+        assert torch.equal(l.wdown, sd[p + "mlp.down_proj.weight"])
+        assert torch.equal(l.ln1, sd[p + "input_layernorm.weight"])
+        assert torch.equal(l.ln2, sd[p + "post_attention_layernorm.weight"])
+    assert all(t.dtype == torch.bfloat16 for t in w._all())
+    # tensor parallel: every rank keeps its Megatron shard of the same checkpoint
+    n = 2
+    for r in range(n):
+        s = ModelWeights.from_hf_dir(m, d, dev, tp_size=n, tp_rank=r)
+        V = m.vocab_size // n
+        assert torch.equal(s.lm_head, head[r * V:(r + 1) * V]) and torch.equal(s.embed, w.embed)
+        for lf, ls in zip(w.layers, s.layers):
+            qs, ks = m.q_size // n, m.kv_size // n
+            assert torch.equal(ls.wqkv, torch.cat([lf.wqkv[r * qs:(r + 1) * qs],
+                                                   lf.wqkv[m.q_size + r * ks: m.q_size + (r + 1) * ks],
+                                                   lf.wqkv[m.q_size + m.kv_size + r * ks: m.q_size + m.kv_size + (r + 1) * ks]]))
+            assert torch.equal(ls.wo, lf.wo[:, r * qs:(r + 1) * qs])
+            rows = 2 * m.intermediate_size // n
+            assert torch.equal(ls.wgu, lf.wgu[r * rows:(r + 1) * rows])
+            assert torch.equal(ls.wdown, lf.wdown[:, r * (m.intermediate_size // n):(r + 1) * (m.intermediate_size // n)])
+
+
+def test_missing_checkpoint_is_a_loud_error(tmp_path, monkeypatch):
+    monkeypatch.delenv("LLM_RANDOM_INIT_SEED", raising=False)
+    monkeypatch.setenv("HF_HUB_OFFLINE", "1")
+    with pytest.raises(FileNotFoundError, match="neither a local directory nor in the HF cache"):
+        resolve_model("meta-llama/Llama-3.1-8B-Instruct-not-here")
+    (tmp_path / "config.json").write_text(json.dumps({"model_type": "llama"}))
+    with pytest.raises(Exception):
+        ModelWeights.from_hf_dir(resolve_model("random:tiny").config, tmp_path, torch.device("cpu"))
