@@ -81,3 +81,48 @@ def test_missing_checkpoint_is_a_loud_error(tmp_path, monkeypatch):
     (tmp_path / "config.json").write_text(json.dumps({"model_type": "llama"}))
     with pytest.raises(Exception):
         ModelWeights.from_hf_dir(resolve_model("random:tiny").config, tmp_path, torch.device("cpu"))
+
+
+def _write_tokenizer(d):
+    """A small byte-level BPE tokenizer in the HF on-disk format with the Llama-3 special tokens and a chat
+    template in tokenizer_config.json (the real files cannot be fetched offline; the format is the same)."""
+    from tokenizers import Tokenizer, decoders, models, pre_tokenizers, trainers
+    from transformers import PreTrainedTokenizerFast
+
+    tok = Tokenizer(models.BPE())
+    tok.pre_tokenizer = pre_tokenizers.ByteLevel(add_prefix_space=False)
+    tok.decoder = decoders.ByteLevel()
+    specials = ["<|begin_of_text|>", "<|end_of_text|>", "<|start_header_id|>", "<|end_header_id|>", "<|eot_id|>"]
+    trainer = trainers.BpeTrainer(vocab_size=400, special_tokens=specials,
+                                  initial_alphabet=pre_tokenizers.ByteLevel.alphabet())
+    tok.train_from_iterator(["the agent asks the tool for the weather in paris", "plan then act then review",
+                             "hello world, hello agents"] * 20, trainer)
+    fast = PreTrainedTokenizerFast(tokenizer_object=tok, bos_token="<|begin_of_text|>", eos_token="<|eot_id|>")
+    fast.chat_template = ("{{ bos_token }}{% for m in messages %}<|start_header_id|>{{ m['role'] }}<|end_header_id|>\n\n"
+                          "{{ m['content'] }}<|eot_id|>{% endfor %}{% if add_generation_prompt %}"
+                          "<|start_header_id|>assistant<|end_header_id|>\n\nCKPT:{% endif %}")
+    fast.save_pretrained(d)
+    return fast
+
+
+def test_checkpoint_tokenizer_and_its_chat_template_are_used(tmp_path):
+    from atx.tokenizer import ByteTokenizer, HFTokenizer, load_tokenizer
+    from llm.backend import B200Backend
+    from tests.fakes import FakeAsyncEngine
+
+    assert isinstance(load_tokenizer(tmp_path, 128256), ByteTokenizer)       # no tokenizer files: offline stub
+    _write_tokenizer(tmp_path)
+    tk = load_tokenizer(tmp_path, 128256)
+    assert isinstance(tk, HFTokenizer)
+    text = "the agent asks the tool"
+    ids = tk.encode(text)
+    assert ids and tk.decode(ids) == text and len(ids) < len(text)           # merges learnt: not byte-per-token
+    eot = tk.tok.convert_tokens_to_ids("<|eot_id|>")
+    assert tk.decode(ids + [eot], skip_special_tokens=True) == text          # `output` carries no special tokens
+    be = B200Backend("ckpt", 256, None, 4, 64, 0.5, engine=FakeAsyncEngine(), tokenizer=tk)
+    assert be.count_tokens(text) == len(ids)
+    templ = be.apply_chat_template("hi", "be brief")
+    # the checkpoint's own template wins over the literal fallback of llm/serve_llm.py:671-678
+    assert templ.endswith("<|start_header_id|>assistant<|end_header_id|>\n\nCKPT:")
+    assert "<|start_header_id|>system<|end_header_id|>\n\nbe brief<|eot_id|>" in templ
+    assert "<|start_header_id|>user<|end_header_id|>\n\nhi<|eot_id|>" in templ
