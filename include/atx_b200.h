@@ -129,6 +129,7 @@ int atx_reduce_scatter_rmsnorm_all_gather(float* x, const void* const* part_ptrs
  *               when the call starts
  *   reset_ptr / reset_bytes  LOCAL region filled with the bf16 sentinel: the OTHER parity's activation rows,
  *               which the GEMMs before this call have finished reading (16-byte multiple)
+ *   clear_buf / clear_rows, zero_ptr / zero_bytes, rows, x, w  as in atx_allreduce_add_rmsnorm (local housekeeping)
  * Calls must alternate between two parities (two rs / out buffer sets), every rank making the same calls in
  * the same order. The whole grid (T x ceil(H/2048) CTAs) spins on remote data and must be co-resident: rejected
  * otherwise. Latency per call, 1 MiB message: see profiles/ (ar_microbench). */
