@@ -155,3 +155,33 @@ def test_scheduler_rejects_oversize_and_aborts_cleanly():
         lone = Scheduler(BlockAllocator(1, 16), 8, 64, 64)
         lone.add(Sequence("l", list(range(40)), SamplingParams(), lone.alloc))
         lone.schedule()
+
+
+def test_block_tables_and_slots_at_the_long_context_config_size():
+    """BASELINE configs[4] at FULL size on the host side: 16 sequences of 32 768 prompt tokens + 128 generated,
+    chunked prefill under an 8192-token budget, 16-token pages, a 73 785-block pool (what the 8B engine sizes on a
+    B200 at 0.92 utilisation). Integer work only, so it is checked exactly: every block table and the slot of
+    every 997th position against the reference model, no block handed out twice, everything returned at the end."""
+    nb, bs, P, O, S = 73785, 16, 32768, 128, 16
+    a = BlockAllocator(nb, bs, enable_prefix_caching=False)
+    ref = RefPagedKV(nb, bs)
+    sched = Scheduler(a, S, 8192, P + O, ())
+    seqs = [Sequence(f"long{i}", [(7 * i + j) % 50000 for j in range(P)],
+                     SamplingParams(temperature=0.0, max_tokens=O, ignore_eos=True), a) for i in range(S)]
+    for s in seqs:
+        sched.add(s)
+    steps = 0
+    while sched.has_work():
+        plan = sched.schedule()
+        assert not plan.empty and sum(c.count for c in plan.prefills) + len(plan.decodes) <= 8192
+        for c in plan.decodes + plan.prefills:      # the reference model grows the same sequences in the same order
+            ref.grow(c.seq.request_id, c.start + c.count)
+            assert c.seq.blocks.table[: len(ref.tables[c.seq.request_id])] == ref.tables[c.seq.request_id]
+            for p in range(c.start, c.start + c.count, 997):
+                assert c.seq.blocks.slots(p, 1)[0] == ref.slot(c.seq.request_id, p)
+        sched.commit(plan, {c.seq.uid: 1 for c in plan.decodes + plan.prefills if c.samples})
+        steps += 1
+    used = [b for t in ref.tables.values() for b in t]
+    assert len(used) == len(set(used)) == S * ((P + O + bs - 1) // bs)       # 2056 pages per sequence, none shared
+    assert all(s.state is SeqState.FINISHED and s.num_generated == O for s in seqs)
+    assert a.num_free == nb and steps >= (S * P) // 8192 + O
