@@ -96,3 +96,92 @@ def test_random_init_tp_shards_are_slices_of_the_single_gpu_model():
                 assert torch.equal(ls.wdown, lf.wdown[:, r * (I // n):(r + 1) * (I // n)])
             V = cfg.vocab_size // n
             assert torch.equal(w.lm_head, full.lm_head[r * V:(r + 1) * V])
+
+
+def _tp_rank_main(rank, world, port, out_q):
+    """One tensor-parallel rank on CPU: the engine's layer schedule (atx/runner.py:_forward) in oracle arithmetic
+    on THIS rank's product-sharded weights, with the exchange step done the way the two-shot kernels do it —
+    rank r owns the token rows t = r (mod world): reduce the partial o_proj / down_proj rows it owns, add its
+    residual rows, normalise, all-gather the normalised rows — over torch.distributed `gloo`."""
+    import os
+
+    import torch.distributed as dist
+
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        shape, cfg = R.shape_by_name("tiny"), model_config_by_name("tiny")
+        sd = R.init_weights(shape, 11)
+        w = ModelWeights.from_state_dict(cfg, sd, torch.device("cpu"), world, rank)
+        T, H, D = 9, cfg.hidden_size, cfg.head_dim
+        hq, hkv = cfg.num_attention_heads // world, cfg.num_key_value_heads // world
+        ids = torch.randint(0, cfg.vocab_size, (T,), generator=torch.Generator().manual_seed(5))
+        cos, sin = R.rope_cos_sin(torch.arange(T), R.llama3_inv_freq(shape))
+        mine = torch.arange(T) % world == rank
+
+        def exchange(h, part, ln):
+            """all-reduce + residual add + RMSNorm, sharded by token row; h keeps only this rank's rows current."""
+            rows = []
+            for owner in range(world):      # reduce-scatter: the owner receives the sum of its rows
+                sel = torch.arange(T) % world == owner
+                buf = part[sel].clone()
+                dist.reduce(buf, dst=owner, op=dist.ReduceOp.SUM)
+                rows.append(buf)
+            h[mine] += rows[rank]
+            normed = R.rms_norm(h[mine], ln.float(), cfg.rms_norm_eps)
+            n_max = (T + world - 1) // world
+            padded = torch.zeros(n_max, H)
+            padded[: normed.shape[0]] = normed
+            gathered = [torch.zeros(n_max, H) for _ in range(world)]
+            dist.all_gather(gathered, padded)
+            xn = torch.zeros(T, H)
+            for owner in range(world):
+                sel = torch.arange(T) % world == owner
+                xn[sel] = gathered[owner][: int(sel.sum())]
+            return xn
+
+        h = w.embed.float()[ids]
+        xn = R.rms_norm(h, w.layers[0].ln1.float(), cfg.rms_norm_eps)       # first norm: local, all rows
+        for li, l in enumerate(w.layers):
+            qkv = xn @ l.wqkv.float().T
+            q = R.apply_rope(qkv[:, : hq * D].view(T, hq, D), cos, sin)
+            k = R.apply_rope(qkv[:, hq * D:(hq + hkv) * D].view(T, hkv, D), cos, sin)
+            v = qkv[:, (hq + hkv) * D:].view(T, hkv, D)
+            attn = R.attention(q, k, v, 0).reshape(T, hq * D)              # this rank's heads only
+            xn = exchange(h, attn @ l.wo.float().T, l.ln2)
+            v64 = l.wgu.float().reshape(-1, 2, 64, H)
+            act = R.swiglu(xn @ v64[:, 0].reshape(-1, H).T, xn @ v64[:, 1].reshape(-1, H).T)
+            nxt = w.layers[li + 1].ln1 if li + 1 < len(w.layers) else w.norm
+            xn = exchange(h, act @ l.wdown.float().T, nxt)
+        part_logits = xn @ w.lm_head.float().T                              # vocabulary shard
+        all_logits = [torch.zeros_like(part_logits) for _ in range(world)]
+        dist.all_gather(all_logits, part_logits)
+        out_q.put((rank, torch.cat(all_logits, dim=1)))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_tp_data_flow_gloo_world2_matches_unsharded_oracle():
+    import socket
+
+    import torch.multiprocessing as tmp
+
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    ctx = tmp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_tp_rank_main, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = dict(q.get(timeout=180) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    shape = R.shape_by_name("tiny")
+    ref = R.RefLlama(shape, R.init_weights(shape, 11))
+    ids = torch.randint(0, shape.vocab_size, (9,), generator=torch.Generator().manual_seed(5))
+    with torch.no_grad():
+        want = ref.forward(ids)
+    assert torch.equal(got[0], got[1])                       # every rank assembles the same logits
+    assert float((got[0] - want).abs().max()) <= 2e-4        # fp32 everywhere: only the summation order differs
