@@ -16,6 +16,7 @@ One step = one forward pass over a flat token batch:
 from __future__ import annotations
 
 import enum
+import hashlib
 import itertools
 import time
 from collections import deque
@@ -36,6 +37,15 @@ class SamplingParams:
     ignore_eos: bool = False
     stop_token_ids: Tuple[int, ...] = ()
     stream: bool = False   # deliver every token to the caller (else: first token, every 32nd, and the last)
+
+
+def default_seed(request_id: str) -> int:
+    """Sampling seed of a request that did not bring one: a hash of its id that is the SAME in every process
+    (Python's own str hash is salted per process). Tensor-parallel ranks build their Sequence objects
+    independently from the broadcast request stream and must draw identical noise from identical logits, or
+    their KV caches and residual shards diverge; it also makes a restarted server repeat itself."""
+    digest = hashlib.blake2b(request_id.encode("utf-8", "surrogatepass"), digest_size=8).digest()
+    return int.from_bytes(digest, "little") & 0x7FFFFFFFFFFFFFFF
 
 
 class SeqState(enum.Enum):
@@ -63,7 +73,7 @@ class Sequence:
         self.finish_reason: Optional[str] = None
         self.arrival = time.monotonic() if arrival is None else arrival
         self.first_token_time: Optional[float] = None
-        self.seed = params.seed if params.seed is not None else (hash(request_id) & 0x7FFFFFFFFFFFFFFF)
+        self.seed = params.seed if params.seed is not None else default_seed(request_id)
         self.num_preemptions = 0
         self.cached_prompt_tokens = 0               # prompt tokens served by the prefix cache
 

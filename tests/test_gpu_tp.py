@@ -13,7 +13,7 @@ pytestmark = pytest.mark.gpu
 GOLD = Path(__file__).parent / "golden"
 
 
-def _rank(rank, world, port, graphs, mode, q):
+def _rank(rank, world, port, graphs, mode, q, temperature=0.0, n_new=16):
     import sys
 
     root = Path(__file__).resolve().parent.parent
@@ -38,7 +38,8 @@ def _rank(rank, world, port, graphs, mode, q):
         eng = LLMEngine(ModelSource(mcfg, None, None),
                         EngineConfig(max_model_len=256, max_num_seqs=4, max_num_batched_tokens=64, num_gpu_blocks=32,
                                      device=rank, tp_size=world, tp_rank=rank, enable_cuda_graphs=graphs), w)
-        seq = eng.add_request("tp", g["prompt"].tolist(), SamplingParams(temperature=0.0, max_tokens=16, ignore_eos=True))
+        seq = eng.add_request("tp", g["prompt"].tolist(), SamplingParams(temperature=temperature, max_tokens=n_new,
+                                                                         ignore_eos=True))
         eng.step()
         first = eng.runner.logits[0].float().cpu().numpy()
         while eng.has_work():
@@ -85,6 +86,39 @@ def test_tp2_matches_hf_golden(graphs, mode):
     assert ids0 == ids1 == gold           # both ranks sample the same tokens, equal to HF greedy
     assert e0 <= 2e-2 and e1 <= 2e-2      # literal north-star bound on this fixture
     assert ar0 > 0
+
+
+def _run_pair(args):
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    ctx = tmp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_rank, args=(r, 2, port, *args[:2], q, *args[2:])) for r in range(2)]
+    for p in procs:
+        p.start()
+    try:
+        got = sorted(q.get(timeout=240) for _ in procs)
+        for p in procs:
+            p.join(timeout=60)
+            assert p.exitcode == 0
+    finally:
+        for p in procs:
+            if p.is_alive():
+                p.kill()
+    return got
+
+
+def test_tp2_ranks_sample_identically_at_the_reference_temperature():
+    """The reference samples at temperature 0.2 with no seed (llm/serve_llm.py:521). Each rank builds its own
+    Sequence for request "tp" in its own spawned process and must draw the same noise: 64 sampled tokens equal
+    on both ranks, and equal again after a restart (fresh processes, different str-hash salts)."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    runs = [_run_pair((True, "ll", 0.2, 64)) for _ in range(2)]
+    for (r0, _, ids0, _, _), (r1, _, ids1, _, _) in runs:
+        assert len(ids0) == 64 and ids0 == ids1
+    assert runs[0][0][2] == runs[1][0][2]
 
 
 def test_tp_server_group_matches_single_engine():

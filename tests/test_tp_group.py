@@ -69,3 +69,43 @@ def test_followers_mirror_rank0_call_for_call(async_sched):
     assert any(m[0] == "abort" for item in group.sent for m in item[1])
     assert not follow.has_work() and not lead.has_work()
     assert follow.allocator.num_used == lead.allocator.num_used
+
+
+def _seed_in_child(rid, conn):
+    from atx.kv_cache import BlockAllocator
+    from atx.scheduler import SamplingParams, Sequence
+
+    conn.send(Sequence(rid, [1, 2, 3], SamplingParams(temperature=0.2), BlockAllocator(4, 16, False)).seed)
+
+
+def test_default_seed_is_the_same_in_every_spawned_process():
+    """Tensor-parallel followers are `spawn`ed processes that build their own Sequence from the broadcast
+    request (atx/tp_group.py:_follower). At the reference's temperature 0.2 (llm/serve_llm.py:521) every rank
+    must draw the same Gumbel noise, so the seed of a request without one cannot come from Python's salted
+    str hash: two fresh interpreters (different PYTHONHASHSEED each) and this one must agree."""
+    import multiprocessing as mp
+    import os
+
+    from atx.kv_cache import BlockAllocator
+    from atx.scheduler import SamplingParams, Sequence, default_seed
+
+    rid = "a3f9c1d2"
+    mine = Sequence(rid, [1, 2, 3], SamplingParams(temperature=0.2), BlockAllocator(4, 16, False)).seed
+    assert mine == default_seed(rid) and 0 <= mine < 2 ** 63
+    assert default_seed("a3f9c1d3") != mine
+    assert Sequence(rid, [1], SamplingParams(seed=0), BlockAllocator(4, 16, False)).seed == 0   # an explicit 0 is kept
+    ctx = mp.get_context("spawn")
+    seen = []
+    for salt in ("1", "2"):
+        os.environ["PYTHONHASHSEED"] = salt
+        try:
+            parent, child = ctx.Pipe()
+            p = ctx.Process(target=_seed_in_child, args=(rid, child))
+            p.start()
+            seen.append(parent.recv())
+            p.join(30)
+        finally:
+            os.environ.pop("PYTHONHASHSEED", None)
+    assert seen == [mine, mine]
+    assert default_seed(rid) == 0x7FFFFFFFFFFFFFFF & int.from_bytes(
+        __import__("hashlib").blake2b(rid.encode(), digest_size=8).digest(), "little")
