@@ -73,6 +73,12 @@ def _follower(rank: int, world: int, port: int, model: str, ecfg: EngineConfig, 
             apply_messages(eng, msg[1])
             if eng.has_work():
                 eng.step()
+    except BaseException as exc:   # device fault, lost pipe: tell rank 0 (it checks before every broadcast)
+        try:
+            conn.send(("fatal", rank, repr(exc)))
+        except (OSError, BrokenPipeError):
+            pass
+        raise
     finally:
         eng.runner.close()
         dist.destroy_process_group()
@@ -113,9 +119,23 @@ class TPGroup:
             raise
 
     def broadcast(self, msgs) -> None:
+        """Raises RuntimeError when a follower has died or reported a failure: the engine thread then fails
+        every waiting request (AsyncEngine._run) instead of launching a step whose peers will never answer."""
         item = ("step", list(msgs))
-        for c in self._conns:
-            c.send(item)
+        for r, (c, p) in enumerate(zip(self._conns, self._procs), start=1):
+            try:
+                if c.poll(0):
+                    msg = c.recv()
+                    if msg and msg[0] == "fatal":
+                        raise RuntimeError(f"tensor-parallel rank {r} failed: {msg[2]}")
+            except (EOFError, OSError) as exc:
+                raise RuntimeError(f"tensor-parallel rank {r} closed its pipe") from exc
+            if not p.is_alive():
+                raise RuntimeError(f"tensor-parallel rank {r} exited (code {p.exitcode})")
+            try:
+                c.send(item)
+            except (OSError, BrokenPipeError) as exc:
+                raise RuntimeError(f"tensor-parallel rank {r} is gone: {exc!r}") from exc
 
     def shutdown(self) -> None:
         for c in self._conns:

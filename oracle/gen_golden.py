@@ -88,3 +88,7 @@ if __name__ == "__main__":
     gold.mkdir(parents=True, exist_ok=True)
     make("tiny", seed=11, prompt_seed=12, prompt_len=40, new_tokens=32, out=gold / "hf_tiny.npz")
     make("tiny128", seed=21, prompt_seed=22, prompt_len=33, new_tokens=32, out=gold / "hf_tiny128.npz")
+    # a prompt long enough for the prefill-sized kernels (persistent tcgen05 GEMM at T > 64, two query tiles
+    # of the tcgen05 attention): what __graft_entry__.smoke() runs. Prompt seed 55 was picked among 23..62 as the
+    # one whose 32-token greedy path has the largest minimum top-1/top-2 margin (0.15) in the fp32 oracle
+    make("tiny128", seed=21, prompt_seed=55, prompt_len=232, new_tokens=32, out=gold / "hf_tiny128_long.npz")

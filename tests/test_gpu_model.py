@@ -43,7 +43,8 @@ def _run_collect(eng, prompt, n_new, temperature=0.0):
     return seq.output_ids, torch.stack(rows)
 
 
-@pytest.mark.parametrize("shape_name,gold,seed", [("tiny", "hf_tiny.npz", 11), ("tiny128", "hf_tiny128.npz", 21)])
+@pytest.mark.parametrize("shape_name,gold,seed", [("tiny", "hf_tiny.npz", 11), ("tiny128", "hf_tiny128.npz", 21),
+                                                  ("tiny128", "hf_tiny128_long.npz", 21)])
 @pytest.mark.parametrize("graphs", [False, True])
 def test_greedy_and_logits_against_hf_golden(shape_name, gold, seed, graphs):
     g = np.load(GOLD / gold)

@@ -109,3 +109,40 @@ def test_default_seed_is_the_same_in_every_spawned_process():
     assert seen == [mine, mine]
     assert default_seed(rid) == 0x7FFFFFFFFFFFFFFF & int.from_bytes(
         __import__("hashlib").blake2b(rid.encode(), digest_size=8).digest(), "little")
+
+
+def _exit_at_once(conn):
+    conn.close()
+
+
+def test_rank0_notices_a_dead_or_failed_follower():
+    """broadcast() runs before every engine-loop iteration of rank 0 (atx/engine.py:_run): a follower that has
+    exited or reported a failure must surface as an error there, not as a step whose peers never answer."""
+    import multiprocessing as mp
+
+    from atx.tp_group import TPGroup
+
+    ctx = mp.get_context("spawn")
+    parent, child = ctx.Pipe(duplex=True)
+    p = ctx.Process(target=_exit_at_once, args=(child,))
+    p.start()
+    p.join(30)
+    child.close()
+    g = object.__new__(TPGroup)
+    g._conns, g._procs = [parent], [p]
+    with pytest.raises(RuntimeError, match="rank 1"):
+        g.broadcast([("abort", "x")])
+
+    class _Alive:
+        exitcode = None
+
+        def is_alive(self):
+            return True
+
+    a, b = ctx.Pipe(duplex=True)
+    g._conns, g._procs = [a], [_Alive()]
+    g.broadcast([("abort", "x")])
+    assert b.recv() == ("step", [("abort", "x")])
+    b.send(("fatal", 1, "RuntimeError('device fault')"))
+    with pytest.raises(RuntimeError, match="device fault"):
+        g.broadcast([])
