@@ -181,8 +181,19 @@ class B200Backend:
         if request_id is None:
             request_id = str(uuid.uuid4())[:8]
         self._resolve_tokenizer()
+        added_bos = 0
         if prompt_ids is None:
             prompt_ids = self._tokenizer.encode(prompt or "", add_special_tokens=False)
+        if prompt is not None:
+            # A TEXT prompt reaches the model the way vLLM feeds it in the reference (llm/serve_llm.py:527 hands
+            # the string to the engine, whose tokenizer adds the special tokens): with <|begin_of_text|> in
+            # front. The chat template already starts with it; raw prompts (skip_chat_template,
+            # LLM_APPLY_CHAT_TEMPLATE=0, /v1/completions) get it here.
+            # `prompt_tokens` keeps counting the text's own tokens, as count_tokens() does (:624-635).
+            bos = getattr(self._tokenizer, "bos_token_id", None)
+            if bos is not None and (len(prompt_ids) == 0 or prompt_ids[0] != bos):
+                prompt_ids = [int(bos)] + list(prompt_ids)
+                added_bos = 1
         if ignore_eos is None:
             ignore_eos = os.environ.get("LLM_IGNORE_EOS", "").lower() in ("1", "true", "yes", "on")
         params = SamplingParams(
@@ -229,7 +240,7 @@ class B200Backend:
                           flush=True)
                     last_log = now
             if final is None:
-                return Generation("", [], len(prompt_ids), queue_wait_s, None)
+                return Generation("", [], len(prompt_ids) - added_bos, queue_wait_s, None)
             ids = list(final.token_ids)
             if log_progress:
                 el = time.monotonic() - t0
@@ -238,7 +249,7 @@ class B200Backend:
             if gen_span is not None and gen_start is not None:
                 gen_span.set_attribute("llm.generate_ms", int((time.monotonic() - gen_start) * 1000))
             text = self._tokenizer.decode(ids, skip_special_tokens=True)
-            return Generation(text, ids, len(prompt_ids), queue_wait_s, final.finish_reason,
+            return Generation(text, ids, len(prompt_ids) - added_bos, queue_wait_s, final.finish_reason,
                               getattr(final, "num_cached_tokens", 0))
         finally:
             if wait_span is not None:

@@ -60,12 +60,13 @@ def burst_prompts(step: int, vocab: int = 128000):
 
 def burst_texts(step: int):
     """Same burst shape as text for the HTTP arm: the offline byte tokenizer maps 1 ASCII char to 1
-    token, so a 1024-char prompt is a 1024-token prompt."""
+    token and the server puts <|begin_of_text|> in front of a raw prompt, so a 1023-char prompt is a
+    1024-token prompt (the shared prefix: 767 chars + that token = 768)."""
     import numpy as np
 
     rng = np.random.default_rng(7 + 1000 * (step + 1000))
     alphabet = np.frombuffer(b"abcdefghijklmnopqrstuvwxyz ABCDEFGHIJKLMNOPQRSTUVWXYZ0123456789.,", dtype=np.uint8)
-    shared = bytes(rng.choice(alphabet, SHARED)).decode()
+    shared = bytes(rng.choice(alphabet, SHARED - 1)).decode()
     return [shared + bytes(rng.choice(alphabet, PROMPT - SHARED)).decode() for _ in range(BATCH)]
 
 
@@ -613,7 +614,7 @@ def main() -> None:
         wall = max_over_ranks(dist, [wall], "cuda")[0]
         flat = [m for burst in metas for m in burst]
         e2e_ttft = gather_over_ranks(dist, [m["queue_wait_s"] for m in flat], world)
-        assert all(m["completion_tokens"] == OUT and m["prompt_tokens"] == PROMPT for m in flat)
+        assert all(m["completion_tokens"] == OUT and m["prompt_tokens"] == PROMPT - 1 for m in flat)
         e2e = {"value": round(tokens / wall, 1), "unit": UNIT,
                "h2d_bytes_per_step": round((r.h2d_bytes - h0) / args.steps),
                "d2h_bytes_per_step": round((r.d2h_bytes - d0) / args.steps),

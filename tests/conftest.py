@@ -15,6 +15,7 @@ for p in (str(ROOT), str(PKG)):
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+    config.addinivalue_line("markers", "slow: minutes of CPU oracle time; skipped unless ATX_RUN_SLOW=1")
 
 
 def pytest_collection_modifyitems(config, items):

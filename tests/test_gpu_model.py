@@ -49,8 +49,11 @@ def _run_collect(eng, prompt, n_new, temperature=0.0):
 def test_greedy_and_logits_against_hf_golden(shape_name, gold, seed, graphs):
     g = np.load(GOLD / gold)
     prompt = g["prompt"].tolist()
-    eng, shape, sd = _engine(shape_name, seed, enable_cuda_graphs=graphs)
+    # the 232-token prompt goes through in ONE chunk: prefill-sized kernels (persistent GEMM, two query tiles)
+    big = dict(max_model_len=512, max_num_batched_tokens=256) if len(prompt) > 64 else {}
+    eng, shape, sd = _engine(shape_name, seed, enable_cuda_graphs=graphs, **big)
     ids, logits = _run_collect(eng, prompt, 32)
+    assert len(ids) == 32
 
     # (1) first-step logits vs the HF fp32 golden vector (literal north_star criterion: 2e-2 max-abs)
     err_first = float((logits[0] - torch.from_numpy(g["logits_last"])).abs().max())
@@ -223,9 +226,17 @@ def test_no_cuda_means_loud_failure(monkeypatch):
         ModelRunner(model_config_by_name("tiny"), EngineConfig(), None)
 
 
-@pytest.mark.parametrize("shape_name,layers", [("1b", 2), ("8b", 1)])
+_FULL_DEPTH = pytest.mark.skipif(__import__("os").environ.get("ATX_RUN_SLOW") != "1",
+                                 reason="full-depth 8B: 32 GB of fp32 oracle weights and minutes of CPU time; "
+                                        "run once on the box with ATX_RUN_SLOW=1 (numbers recorded in DESIGN.md)")
+
+
+@pytest.mark.parametrize("shape_name,layers", [("1b", 2), ("8b", 1), ("70b", 1),
+                                               pytest.param("1b", 16, marks=[pytest.mark.slow, _FULL_DEPTH]),
+                                               pytest.param("8b", 32, marks=[pytest.mark.slow, _FULL_DEPTH])])
 def test_baseline_shapes_full_width_reduced_depth(shape_name, layers):
-    """The BASELINE.json model shapes at FULL width — hidden size, GQA head counts, head_dim 64 (1B) / 128 (8B),
+    """The BASELINE.json model shapes at FULL width — hidden size, GQA head counts (group 4; group 8 with 64 query
+    heads, hidden 8192 and a 28 672-wide MLP for the 70B shape), head_dim 64 (1B) / 128 (8B, 70B),
     the 128 256-token vocabulary (1002 LM-head tiles, the sampler over a real row), tied (1B) / untied (8B) head,
     llama3 rope scaling x32 / x8 — at reduced depth so the fp32 oracle finishes in seconds, on
     BASELINE configs[0]'s input: batch 1, a 128-token prompt of ids below 128 000, greedy decoding.
@@ -244,7 +255,8 @@ def test_baseline_shapes_full_width_reduced_depth(shape_name, layers):
                                  async_scheduling=False), w)
     g = torch.Generator().manual_seed(1)
     prompt = torch.randint(0, 128000, (128,), generator=g).tolist()
-    n_new = 8
+    full_depth = layers >= 16
+    n_new = 32 if full_depth else 8   # full depth (SURVEY 8c "once on the box"): the north star's 32 tokens
     ids, logits = _run_collect(eng, prompt, n_new)
     assert logits.shape == (n_new, 128256)
     exact = R.RefLlama(shape, sd)
@@ -270,5 +282,14 @@ def test_baseline_shapes_full_width_reduced_depth(shape_name, layers):
     # roundings of intermediate activations) and must not exceed it by much; nor may the total.
     assert err_emul <= 1.5 * hf_bf16_vs_fp32 + 1e-2, (err_emul, hf_bf16_vs_fp32)
     assert err_exact <= 2.0 * hf_bf16_vs_fp32 + 1e-2, (err_exact, hf_bf16_vs_fp32)
+    if full_depth:
+        with torch.no_grad():
+            hf_greedy, _ = R.RefLlama(shape, sd).greedy(torch.tensor(prompt), n_new)
+        n_same = next((i for i, (a, b) in enumerate(zip(ids, hf_greedy)) if a != b), n_new)
+        rms = float((logits - lo_exact).pow(2).mean().sqrt())
+        print(f"[{shape_name} x{layers}] literal north-star criteria: logits max-abs vs fp32 {err_exact:.4f} "
+              f"(bound 2e-2: {'met' if err_exact <= 2e-2 else 'NOT met'}; rms {rms:.4f}); free-running greedy "
+              f"identical to the fp32 oracle for {n_same}/{n_new} tokens; teacher-forced arg-max agreement "
+              f"{int((logits.argmax(-1) == lo_exact.argmax(-1)).sum())}/{n_new}")
     assert torch.equal(logits.argmax(-1)[safe], lo_exact.argmax(-1)[safe])
     assert ids == logits.argmax(-1).tolist()                # the sampler's arg-max over the full 128 256-wide row

@@ -70,8 +70,12 @@ def test_chat_template_is_the_reference_fallback_string(served):
     assert tok.decode(eng.seen[-1]["ids"]) == GOLD["template_case"]["formatted"]
     _post(client, loop, "/chat", json={"prompt": GOLD["template_case"]["prompt"]})
     assert tok.decode(eng.seen[-1]["ids"]) == GOLD["template_case"]["formatted_default_system"]
+    # a raw prompt reaches the model as vLLM would feed it: <|begin_of_text|> first (exactly once), then the text
     _post(client, loop, "/chat", json={"input": "raw", "skip_chat_template": True})
-    assert tok.decode(eng.seen[-1]["ids"]) == "raw"
+    ids = eng.seen[-1]["ids"]
+    assert ids[0] == tok.bos_token_id and tok.decode(ids[1:]) == "raw"
+    _post(client, loop, "/chat", json={"input": "<|begin_of_text|>raw", "skip_chat_template": True})
+    assert eng.seen[-1]["ids"] == ids
 
 
 def test_error_bodies_and_status_codes(served):
@@ -170,7 +174,8 @@ def test_prompt_truncation_keeps_head(served, monkeypatch):
     monkeypatch.setattr(S, "LLM_MAX_MODEL_LEN", 300)
     monkeypatch.setattr(S, "LLM_PROMPT_SAFETY_MARGIN_TOKENS", 28)
     st, body, _ = _post(client, loop, "/chat", json={"prompt": "z" * 1000, "max_tokens": 72, "skip_chat_template": True})
-    assert st == 200 and len(eng.seen[-1]["ids"]) == 200  # 300 - 72 - 28
+    assert st == 200 and len(eng.seen[-1]["ids"]) == 201  # 300 - 72 - 28 text tokens after <|begin_of_text|>
+    assert eng.seen[-1]["ids"][1:] == [ord("z")] * 200
     assert body["meta"]["otel"]["attributes"]["app.prompt_truncated"] is True
     assert body["meta"]["otel"]["attributes"]["app.prompt_truncated_tokens"] == 800
     assert body["meta"]["prompt_tokens"] == 200
@@ -192,7 +197,7 @@ def test_openai_chat_completions_shape(served):
     st, body, _ = _post(client, loop, "/v1/chat/completions", json={"messages": []})
     assert st == 400 and body == {"error": "Field 'messages' must be a non-empty list"}
     st, body, _ = _post(client, loop, "/v1/completions", json={"prompt": "abc", "max_tokens": 1})
-    assert st == 200 and body["object"] == "text_completion" and tok.decode(eng.seen[-1]["ids"]) == "abc"
+    assert st == 200 and body["object"] == "text_completion" and tok.decode(eng.seen[-1]["ids"][1:]) == "abc"
 
 
 def test_chat_streaming_sse(served):
