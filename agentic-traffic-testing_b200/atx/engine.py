@@ -112,7 +112,7 @@ class LLMEngine:
         if self._inflight is None:
             plan = self.scheduler.schedule()
             if plan.empty:
-                return []
+                return list(plan.finished)   # sequences the scheduler had to end (they outgrew the KV pool)
             if self.batch_size_observer is not None:
                 self.batch_size_observer(len(plan.decodes) + len(plan.prefills))
             self._inflight = (plan, self.runner.launch(plan))
@@ -128,7 +128,7 @@ class LLMEngine:
         self.steps += 1
         touched = self.scheduler.commit(plan, sampled)
         self._inflight = nxt
-        return touched
+        return touched + plan.finished
 
     def generate_sync(self, prompts: List[Seq[int]], params: SamplingParams) -> List[List[int]]:
         """Blocking helper for tests and the bench: run the given prompts to completion."""

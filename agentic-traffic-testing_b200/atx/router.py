@@ -16,6 +16,7 @@ from __future__ import annotations
 
 import asyncio
 import multiprocessing as mp
+import queue
 import threading
 from typing import AsyncIterator, Callable, Dict, List, Optional, Sequence as Seq
 
@@ -42,6 +43,8 @@ def _engine_worker(rank: int, model: str, ecfg: EngineConfig, req, resp) -> None
     except BaseException as exc:  # no GPU / no library: report, never hang the parent
         resp.send(("fatal", rank, repr(exc)))
         return
+    batch_sizes: List[int] = []          # scheduler batch size of every step since the last stats message
+    eng.batch_size_observer = batch_sizes.append
     while True:
         block = not eng.has_work()
         while req.poll(None if block else 0):
@@ -66,8 +69,9 @@ def _engine_worker(rank: int, model: str, ecfg: EngineConfig, req, resp) -> None
                 out = seq.output_ids
                 resp.send(("out", seq.request_id, out, fin, seq.finish_reason, seq.prompt_len,
                            seq.cached_prompt_tokens))
-            if eng.steps % 16 == 0:
-                resp.send(("stats", rank, eng.allocator.num_used))
+            if eng.steps % 16 == 0 or not eng.has_work():
+                resp.send(("stats", rank, eng.allocator.num_used, batch_sizes[:]))
+                batch_sizes.clear()
         except BaseException as exc:
             resp.send(("fatal", rank, repr(exc)))
             return
@@ -79,6 +83,7 @@ class Router:
     def __init__(self, n: int, block_size: int):
         self.n, self.bs = n, block_size
         self.load = [0] * n                      # outstanding tokens (prompt + max new) per replica
+        self.alive = [True] * n                  # a replica whose process died takes no more requests
         self._home: Dict[bytes, int] = {}
 
     def _key(self, ids: Seq[int]) -> Optional[bytes]:
@@ -91,12 +96,15 @@ class Router:
         return key
 
     def pick(self, ids: Seq[int], cost: int) -> int:
-        lightest = min(range(self.n), key=lambda r: (self.load[r], r))
+        live = [r for r in range(self.n) if self.alive[r]]
+        if not live:
+            raise RuntimeError("no engine replica is alive")
+        lightest = min(live, key=lambda r: (self.load[r], r))
         key = self._key(ids)
         choice = lightest
         if key is not None:
             home = self._home.get(key)
-            if home is not None and self.load[home] <= SPILL_FACTOR * self.load[lightest] + cost:
+            if home is not None and self.alive[home] and self.load[home] <= SPILL_FACTOR * self.load[lightest] + cost:
                 choice = home
             self._home[key] = choice
             if len(self._home) > 65536:
@@ -106,6 +114,10 @@ class Router:
 
     def done(self, replica: int, cost: int) -> None:
         self.load[replica] = max(0, self.load[replica] - cost)
+
+    def mark_dead(self, replica: int) -> None:
+        self.alive[replica] = False
+        self.load[replica] = 0
 
 
 class ReplicaPool:
@@ -139,8 +151,12 @@ class ReplicaPool:
         self._used = [0] * n
         self._batch_observer = None
         self._stop = False
+        # pipe writes happen on one writer thread per replica: a busy replica with a full pipe must never block
+        # the HTTP server's event loop (the 64 KiB pipe buffer holds only a few long prompts)
+        self._outq: List[queue.Queue] = [queue.Queue() for _ in range(n)]
         self._readers = [threading.Thread(target=self._read, args=(r,), daemon=True) for r in range(n)]
-        for t in self._readers:
+        self._writers = [threading.Thread(target=self._write, args=(r,), daemon=True) for r in range(n)]
+        for t in self._readers + self._writers:
             t.start()
 
     # ---- front-door API (same as AsyncEngine) ----------------------------------------------------------
@@ -151,9 +167,9 @@ class ReplicaPool:
         with self._lock:
             if request_id in self._streams:
                 raise ValueError(f"duplicate request id {request_id!r}")
-            rep = self.router.pick(prompt_ids, cost)
+            rep = self.router.pick(prompt_ids, cost)      # raises when every replica has died
             self._streams[request_id] = (loop, q, rep, cost, [])
-            self._req[rep].send(("add", request_id, list(prompt_ids), params))
+        self._outq[rep].put(("add", request_id, list(prompt_ids), params))
         finished = False
         try:
             while True:
@@ -166,10 +182,34 @@ class ReplicaPool:
                     return
         finally:
             with self._lock:
-                if self._streams.pop(request_id, None) is not None:
+                mine = self._streams.pop(request_id, None)
+                if mine is not None and self.router.alive[rep]:
                     self.router.done(rep, cost)
-                    if not finished:
-                        self._req[rep].send(("abort", request_id))
+            if mine is not None and not finished and self.router.alive[rep]:
+                self._outq[rep].put(("abort", request_id))
+
+    def _write(self, r: int) -> None:
+        conn = self._req[r]
+        while True:
+            msg = self._outq[r].get()
+            if msg is None:
+                return
+            try:
+                conn.send(msg)
+            except (OSError, BrokenPipeError, ValueError) as exc:
+                self._replica_died(r, f"pipe to replica closed: {exc!r}")
+                return
+
+    def _replica_died(self, r: int, why: str) -> None:
+        """Fail every request the replica holds, and route nothing more to it."""
+        with self._lock:
+            if not self.router.alive[r]:
+                return
+            self.router.mark_dead(r)
+            mine = [s for s in self._streams.values() if s[2] == r]
+        print(f"[atx] replica {r} is gone ({why}); {sum(self.router.alive)} of {self.n} left", flush=True)
+        for loop, q, *_ in mine:
+            loop.call_soon_threadsafe(q.put_nowait, RuntimeError(f"replica {r} failed: {why}"))
 
     def _read(self, r: int) -> None:
         conn = self._resp[r]
@@ -196,11 +236,14 @@ class ReplicaPool:
                     st[0].call_soon_threadsafe(st[1].put_nowait, ValueError(msg[2]))
             elif kind == "stats":
                 self._used[r] = msg[2]
+                obs = self._batch_observer
+                if obs is not None and len(msg) > 3:
+                    for b in msg[3]:
+                        obs(b)
             elif kind == "fatal":
-                with self._lock:
-                    mine = [s for s in self._streams.values() if s[2] == r]
-                for loop, q, *_ in mine:
-                    loop.call_soon_threadsafe(q.put_nowait, RuntimeError(f"replica {r} failed: {msg[2]}"))
+                if not self._stop:
+                    self._replica_died(r, msg[2])
+                self._outq[r].put(None)
                 return
 
     # ---- facts for the gauges: per-replica values summed (documented in DESIGN.md) -------------------------
@@ -208,18 +251,19 @@ class ReplicaPool:
         return sum(k[0] for k in self._kv), self._kv[0][1]
 
     def set_batch_size_observer(self, fn) -> None:
-        self._batch_observer = fn  # replicas do not stream batch sizes; kept for interface parity
+        """`fn(batch_size)` per scheduler step of every replica (they arrive in bundles with the stats message)."""
+        self._batch_observer = fn
 
     def stats(self) -> dict:
         return {"kv_used_blocks": sum(self._used), "replica_load": list(self.router.load)}
 
     def shutdown(self) -> None:
         self._stop = True
-        for c in self._req:
-            try:
-                c.send(("stop",))
-            except Exception:
-                pass
+        for r in range(self.n):
+            self._outq[r].put(("stop",))
+            self._outq[r].put(None)
+        for t in self._writers:
+            t.join(timeout=5)
         for p in self._procs:
             p.join(timeout=5)
             if p.is_alive():

@@ -104,6 +104,7 @@ class StepPlan:
     decodes: List[Chunk] = field(default_factory=list)
     prefills: List[Chunk] = field(default_factory=list)
     preempted: List[Sequence] = field(default_factory=list)
+    finished: List[Sequence] = field(default_factory=list)   # ended by the scheduler itself (KV pool too small)
 
     @property
     def num_tokens(self) -> int:
@@ -176,7 +177,10 @@ class Scheduler:
                 except OutOfBlocks:
                     victim = self.running[-1]
                     if victim is seq and len(self.running) == 1:
-                        raise OutOfBlocks("a single sequence does not fit the KV cache")
+                        # alone in the pool and still out of blocks: this sequence has outgrown the KV cache.
+                        # It ends here with what it has ("length"), the engine and every other request live on.
+                        self._retire_oversized(seq, plan)
+                        break
                     self._preempt(victim, plan)
                     plan.decodes = [c for c in plan.decodes if c.seq is not victim]
                     if victim is seq:
@@ -229,16 +233,31 @@ class Scheduler:
             self.running.append(seq)
             budget -= used
         if plan.empty and not self.running and self.waiting:
-            raise OutOfBlocks("the sequence at the head of the queue can never fit the KV cache")
+            # nothing else holds a block and the head of the queue still does not fit: it never will
+            self._retire_oversized(self.waiting.popleft(), plan)
+            return self._again(plan)
         if plan.empty and self.running:
             # every running sequence is stuck mid-prompt on an exhausted pool: evict the youngest
             if len(self.running) == 1:
-                raise OutOfBlocks("a single sequence does not fit the KV cache")
-            self._preempt(self.running[-1], plan)
-            again = self.schedule()
-            again.preempted = plan.preempted + again.preempted
-            return again
+                self._retire_oversized(self.running[0], plan)
+            else:
+                self._preempt(self.running[-1], plan)
+            return self._again(plan)
         return plan
+
+    def _retire_oversized(self, seq: Sequence, plan: StepPlan) -> None:
+        if seq in self.running:
+            self.running.remove(seq)
+        self._finish(seq, "length")
+        plan.finished.append(seq)
+
+    def _again(self, plan: StepPlan) -> StepPlan:
+        if not self.has_work():
+            return plan
+        again = self.schedule()
+        again.preempted = plan.preempted + again.preempted
+        again.finished = plan.finished + again.finished
+        return again
 
     # ---- after the forward pass -----------------------------------------------------------------------
     def commit(self, plan: StepPlan, sampled: Dict[int, int], now: Optional[float] = None) -> List[Sequence]:

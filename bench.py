@@ -212,19 +212,29 @@ def gemm_roofline(engine, T: int, hbm_gbs: float) -> dict:
             "launches_per_decode_step": launches}
 
 
-def build_cpu_reference(threads: int, layers: int = 32):
+_CPU_SHAPES = {
+    "8b": dict(hidden_size=4096, intermediate_size=14336, num_hidden_layers=32, num_attention_heads=32,
+               num_key_value_heads=8, head_dim=128, tie_word_embeddings=False, factor=8.0),
+    "1b": dict(hidden_size=2048, intermediate_size=8192, num_hidden_layers=16, num_attention_heads=32,
+               num_key_value_heads=8, head_dim=64, tie_word_embeddings=True, factor=32.0),
+}
+
+
+def build_cpu_reference(threads: int, shape: str = "8b", layers=None):
     """The reference's CPU model (llm/hf_cpu_server.py:39-50): transformers LlamaForCausalLM, fp32, device=cpu,
-    8B shape, cheap random fill (values do not affect CPU speed)."""
+    Llama-3.1-8B / Llama-3.2-1B shape, cheap random fill (values do not affect CPU speed)."""
     import torch
     from transformers import LlamaConfig, LlamaForCausalLM
     from transformers.models.llama.modeling_llama import LlamaRotaryEmbedding
 
     torch.set_num_threads(threads)
-    cfg = LlamaConfig(vocab_size=128256, hidden_size=4096, intermediate_size=14336, num_hidden_layers=layers,
-                      num_attention_heads=32, num_key_value_heads=8, head_dim=128, rms_norm_eps=1e-5,
-                      rope_theta=500000.0, max_position_embeddings=131072, tie_word_embeddings=False,
-                      rope_scaling={"rope_type": "llama3", "factor": 8.0, "low_freq_factor": 1.0,
-                                    "high_freq_factor": 4.0, "original_max_position_embeddings": 8192})
+    sh = dict(_CPU_SHAPES[shape])
+    factor = sh.pop("factor")
+    if layers:
+        sh["num_hidden_layers"] = layers
+    cfg = LlamaConfig(vocab_size=128256, rms_norm_eps=1e-5, rope_theta=500000.0, max_position_embeddings=131072,
+                      rope_scaling={"rope_type": "llama3", "factor": factor, "low_freq_factor": 1.0,
+                                    "high_freq_factor": 4.0, "original_max_position_embeddings": 8192}, **sh)
     with torch.device("meta"):
         model = LlamaForCausalLM(cfg)
     model = model.to_empty(device="cpu").to(torch.float32)
@@ -238,42 +248,84 @@ def build_cpu_reference(threads: int, layers: int = 32):
         n = flat.numel() // k * k
         flat[:n].view(-1, k).copy_(tile)
         flat[n:].copy_(tile[: flat.numel() - n])
+    if cfg.tie_word_embeddings:
+        model.tie_weights()
     model.model.rotary_emb = LlamaRotaryEmbedding(config=cfg, device="cpu")
     model.eval()
     return model
 
 
-def cpu_reference_sample(threads: int, prompt_len: int = 64, new_tokens: int = 4, layers: int = 32, model=None):
-    """One bounded sample of the burst on the reference's CPU path (same model shape and batch; shorter
-    prompt, fewer new tokens). Greedy instead of the reference's temperature=0.7 sampling: same arithmetic
-    per token."""
+def cpu_generate(model, ids, new_tokens: int):
+    """Greedy generation exactly as HF's generate(do_sample=False, min_new_tokens=new_tokens) computes it
+    (one prompt pass, then one cached step per token), with prefill and decode timed separately."""
     import torch
 
-    if model is None:
-        model = build_cpu_reference(threads, layers)
-    g = torch.Generator().manual_seed(2)
-    ids = torch.randint(0, 128000, (BATCH, prompt_len), generator=g)
     with torch.no_grad():
         t1 = time.perf_counter()
         out = model(ids, use_cache=True)
+        past, nxt = out.past_key_values, out.logits[:, -1].argmax(-1, keepdim=True)   # token 1 comes from the prompt pass
         t2 = time.perf_counter()
-        past, nxt = out.past_key_values, out.logits[:, -1].argmax(-1, keepdim=True)
-        for _ in range(new_tokens):
+        for _ in range(new_tokens - 1):
             out = model(nxt, past_key_values=past, use_cache=True)
             past, nxt = out.past_key_values, out.logits[:, -1].argmax(-1, keepdim=True)
         t3 = time.perf_counter()
-    prefill_s, decode_s = t2 - t1, t3 - t2
-    per_step = decode_s / new_tokens
-    est_full = prefill_s * (PROMPT / prompt_len) + per_step * OUT  # GEMM-dominated: linear in tokens
-    return {"value": round(BATCH * new_tokens / (prefill_s + decode_s), 3), "unit": UNIT, "cores": threads,
-            "kind": "reference",
-            "sample": (f"transformers.LlamaForCausalLM fp32 on CPU (the class llm/hf_cpu_server.py:39-50 loads), "
-                       f"8B shape x {layers} layers, batch {BATCH}, {prompt_len}-token prompts, {new_tokens} greedy "
-                       f"tokens; prefill {prefill_s:.2f}s, decode {per_step:.3f}s/step"),
+    return t2 - t1, t3 - t2
+
+
+# one step of the reference arm = one bounded sample of the burst: same model, same batch of 6, the workload's
+# 4:1 prompt:output ratio at 1/32 of its length (the full burst is ~150 s of CPU work per step)
+SAMPLE_PROMPT, SAMPLE_OUT = 32, 8
+
+
+def cpu_burst_sample(model, seed: int, prompt_len: int = SAMPLE_PROMPT, new_tokens: int = SAMPLE_OUT):
+    import torch
+
+    g = torch.Generator().manual_seed(2 + seed)
+    ids = torch.randint(0, 128000, (BATCH, prompt_len), generator=g)
+    return cpu_generate(model, ids, new_tokens)
+
+
+def sample_text(prompt_len: int, new_tokens: int, k: int, w: int) -> str:
+    return (f"transformers.LlamaForCausalLM fp32 on CPU (the class llm/hf_cpu_server.py:39-50 loads, greedy instead of "
+            f"its temperature-0.7 sampling: same arithmetic per token), Llama-3.1-8B shape x 32 layers, batch {BATCH}, "
+            f"{prompt_len}-token prompts + {new_tokens} tokens each per step (the burst's 4:1 prompt:output ratio at "
+            f"1/{PROMPT // prompt_len} length; the full 1024 + 256 burst is minutes of CPU work per step); "
+            f"{k} timed step(s) after {w} warm-up")
+
+
+def cpu_baseline_record(threads: int, samples, k: int, w: int, prompt_len: int, new_tokens: int) -> dict:
+    pf = sum(s[0] for s in samples)
+    dec = sum(s[1] for s in samples)
+    tok = BATCH * new_tokens * len(samples)
+    per_step = dec / (len(samples) * max(1, new_tokens - 1))
+    pf_per_tok = pf / (len(samples) * BATCH * prompt_len)
+    est_full = pf_per_tok * BATCH * PROMPT + per_step * (OUT - 1)
+    return {"value": round(tok / (pf + dec), 3), "unit": UNIT, "cores": threads, "kind": "reference",
+            "sample": sample_text(prompt_len, new_tokens, k, w),
+            "prefill_s_per_step": round(pf / len(samples), 3), "decode_s_per_token_step": round(per_step, 4),
             "decode_only_tokens_per_s": round(BATCH / per_step, 3),
             "extrapolated_full_workload_tokens_per_s": round(BATCH * OUT / est_full, 3),
-            "extrapolated_full_workload_ttft_s": round(prefill_s * (PROMPT / prompt_len), 2),
-            "_tokens": BATCH * new_tokens, "_seconds": prefill_s + decode_s}
+            "extrapolated_full_workload_ttft_s": round(pf_per_tok * BATCH * PROMPT, 2)}
+
+
+def cpu_config1(threads: int) -> dict:
+    """BASELINE.json configs[0] exactly: Llama-3.2-1B shape, fp32, batch 1, prompt
+    randint(0, 128000, (1, 128)) seed 1, 64 greedy tokens (EOS cannot shorten it), prefill and decode timed
+    separately; host DRAM GB/s = 4.94 GB of fp32 weights streamed per decoded token."""
+    import torch
+
+    model = build_cpu_reference(threads, "1b")
+    g = torch.Generator().manual_seed(1)
+    ids = torch.randint(0, 128000, (1, 128), generator=g)
+    cpu_generate(model, ids[:, :16], 2)                      # page-in / thread-pool warm-up
+    pf, dec = cpu_generate(model, ids, 64)
+    wbytes = sum(p.numel() for p in model.parameters()) * 4  # tied head counted once: 1.236 G params = 4.94 GB
+    return {"workload": "BASELINE configs[0]: Llama-3.2-1B shape random init, fp32 CPU, batch 1, 128-token prompt "
+                        "(seed 1), 64 greedy tokens",
+            "cores": threads, "prefill_s": round(pf, 3), "decode_s": round(dec, 3),
+            "tokens_per_s": round(64 / (pf + dec), 2), "decode_tokens_per_s": round(63 / dec, 2),
+            "prefill_tokens_per_s": round(128 / pf, 1), "weight_gb": round(wbytes / 1e9, 3),
+            "host_dram_gbs": round(wbytes / 1e9 * 63 / dec, 1)}
 
 
 # ------------------------------------------------------------------------------------------------------
@@ -480,7 +532,7 @@ def main() -> None:
     ap.add_argument("--trace-out", default="", help="directory for response.json / llm_calls.jsonl of a trace replay")
     ap.add_argument("--long-out", type=int, default=128)
     ap.add_argument("--tp-out", type=int, default=256)
-    ap.add_argument("--layers", type=int, default=None, help="tp70b only: reduce depth for smoke runs")
+    ap.add_argument("--layers", type=int, default=None, help="tp70b / --impl reference: reduce depth for smoke runs")
     ap.add_argument("--tp-prefetch-ab", default="", help="tp70b only: comma-separated ATX_TP_L2_PREFETCH_KB values "
                                                          "to time after the main measurement")
     args = ap.parse_args()
@@ -493,26 +545,36 @@ def main() -> None:
         # The reference's own CPU implementation of the path, timed on this box's host cores. Rank 0 only.
         if rank != 0:
             return
-        model = build_cpu_reference(threads)
-        for _ in range(min(args.warmup, 1)):          # one warm-up sample (page-in, thread pool)
-            cpu_reference_sample(threads, model=model)
-        k = max(1, min(args.steps, 3))                 # each sample is ~10-20 s of CPU work
-        samples = [cpu_reference_sample(threads, model=model) for _ in range(k)]
-        tok = sum(s["_tokens"] for s in samples)
-        sec = sum(s["_seconds"] for s in samples)
-        best = dict(samples[0], value=round(tok / sec, 3))
-        for s_ in samples:
-            s_.pop("_tokens"), s_.pop("_seconds")
-        best.pop("_tokens", None), best.pop("_seconds", None)
-        best["sample"] += f"; {k} timed sample(s) after {min(args.warmup, 1)} warm-up"
+        model = build_cpu_reference(threads, layers=args.layers)   # --layers: reduced depth, smoke runs only
+        K, W = max(1, args.steps), max(0, args.warmup)
+        pl, nt = SAMPLE_PROMPT, SAMPLE_OUT
+        probe = cpu_burst_sample(model, -1, 8, 2)           # page-in + a rate estimate (not counted)
+        est = probe[0] * pl / 8 + probe[1] * (nt - 1)
+        while est * (K + W) > 240.0 and nt > 1:              # keep the whole run within a few minutes
+            pl, nt = pl // 2, nt // 2
+            est = probe[0] * pl / 8 + probe[1] * max(1, nt - 1)
+        for w in range(W):
+            cpu_burst_sample(model, 1000 + w, pl, nt)
+        t0 = time.perf_counter()
+        samples = [cpu_burst_sample(model, k, pl, nt) for k in range(K)]
+        wall = time.perf_counter() - t0
+        rec = cpu_baseline_record(threads, samples, K, W, pl, nt)
+        rec["value"] = round(BATCH * nt * K / wall, 3)       # wall clock over exactly K steps
+        if args.layers:
+            rec["sample"] += f" [SMOKE RUN: {args.layers} layers only]"
+        del model
+        try:
+            c1 = cpu_config1(threads)
+        except Exception as exc:
+            c1 = {"failed": f"{type(exc).__name__}: {exc}"}
         print(json.dumps({
-            "impl": "reference", "metric": METRIC, "value": best["value"], "unit": UNIT, "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(1e3 * sec / k, 1), "higher_is_better": True,
+            "impl": "reference", "metric": METRIC, "value": rec["value"], "unit": UNIT, "n_gpus": args.gpus,
+            "steps": K, "warmup": W, "ms_per_step": round(1e3 * wall / K, 1), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD_TEXT, "parallelism": f"cpu x{threads} threads",
-                       "note": "each step is a bounded sample of the workload (see cpu_baseline.sample)"},
-            "cpu_baseline": best,
-            "e2e": {"value": best["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                       "sample": rec["sample"], "tokens_per_step": BATCH * nt},
+            "cpu_baseline": rec, "config1_cpu": c1,
+            "e2e": {"value": rec["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         }))
         return
 
@@ -624,8 +686,12 @@ def main() -> None:
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
-            cpu = cpu_reference_sample(threads)
-            cpu.pop("_tokens", None), cpu.pop("_seconds", None)
+            model = build_cpu_reference(threads)
+            cpu_burst_sample(model, -1, 8, 2)
+            samples = [cpu_burst_sample(model, k) for k in range(2)]
+            cpu = cpu_baseline_record(threads, samples, 2, 1, SAMPLE_PROMPT, SAMPLE_OUT)
+            del model
+            cpu["config1"] = cpu_config1(threads)
         except Exception as exc:  # e.g. not enough host RAM for 32 GB of fp32 weights
             cpu = {"value": None, "unit": UNIT, "cores": threads, "kind": "reference",
                    "sample": f"failed: {type(exc).__name__}: {exc}"}

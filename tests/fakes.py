@@ -51,9 +51,13 @@ def fake_replica_worker(rank, model, ecfg, req, resp):
             return
         if msg[0] == "add":
             _, rid, ids, params = msg
-            if model == "explode":
+            if model == "explode" or (model == "explode1" and rank == 1):
                 resp.send(("fatal", rank, "boom"))
                 return
+            if model == "vanish1" and rank == 1:     # the process dies without a word (OOM kill, segfault)
+                import os
+
+                os._exit(3)
             if len(ids) > 500:
                 resp.send(("error", rid, "ValueError('too long')"))
                 continue
@@ -61,6 +65,7 @@ def fake_replica_worker(rank, model, ecfg, req, resp):
             for i in range(n):
                 toks = [1000 * rank + j for j in range(i + 1)]
                 resp.send(("out", rid, toks, i == n - 1, "length" if i == n - 1 else None, len(ids), 0))
+            resp.send(("stats", rank, 7 + rank, [1, 2, 2]))    # KV blocks in use + the batch size of three steps
 
 
 class _LogicRunner:

@@ -151,10 +151,38 @@ def test_scheduler_rejects_oversize_and_aborts_cleanly():
     sched.commit(plan, {s.uid: 1})
     assert a.num_used == 2
     assert sched.abort("x") is s and s.finish_reason == "abort" and a.num_used == 0 and not sched.has_work()
-    with pytest.raises(OutOfBlocks):
-        lone = Scheduler(BlockAllocator(1, 16), 8, 64, 64)
-        lone.add(Sequence("l", list(range(40)), SamplingParams(), lone.alloc))
-        lone.schedule()
+
+
+def test_a_sequence_that_outgrows_the_kv_pool_ends_with_length_and_nobody_else_suffers():
+    """One long generation on a small pool must not take the engine down (it used to raise OutOfBlocks out of
+    the step loop, which failed every in-flight request): the sequence that cannot grow even when it is alone
+    ends with finish_reason "length" and keeps its tokens; a prompt that cannot fit even an empty pool ends
+    with no tokens; requests queued behind them run normally."""
+    from tests.fakes import make_logic_engine
+
+    # (a) prompt that never fits: 40 tokens, 1 block
+    lone = Scheduler(BlockAllocator(1, 16), 8, 64, 64)
+    big = Sequence("l", list(range(40)), SamplingParams(), lone.alloc)
+    lone.add(big)
+    plan = lone.schedule()
+    assert plan.empty and plan.finished == [big] and big.finish_reason == "length" and big.num_generated == 0
+    assert not lone.has_work() and lone.alloc.num_used == 0
+
+    # (b) through LLMEngine.step(): 4 blocks = 64 tokens of KV; `hog` wants 20 + 100 tokens, `ok` waits behind it
+    eng = make_logic_engine(max_num_seqs=1, max_num_batched_tokens=48, max_model_len=256, num_blocks=4,
+                            async_scheduling=True)
+    hog = eng.add_request("hog", list(range(20)), SamplingParams(max_tokens=100, ignore_eos=True))
+    ok = eng.add_request("ok", list(range(100, 110)), SamplingParams(max_tokens=5, ignore_eos=True))
+    reported = []
+    steps = 0
+    while eng.has_work():
+        reported += [s.request_id for s in eng.step() if s.state is SeqState.FINISHED]
+        steps += 1
+        assert steps < 500
+    assert hog.finish_reason == "length" and 40 <= hog.num_generated <= 45     # filled the 64-token pool, then ended
+    assert ok.finish_reason == "length" and ok.num_generated == 5
+    assert sorted(reported) == ["hog", "ok"]                                  # both reach their callers
+    assert eng.allocator.num_used == 0
 
 
 def test_block_tables_and_slots_at_the_long_context_config_size():

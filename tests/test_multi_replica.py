@@ -76,6 +76,37 @@ def test_replica_failure_fails_waiters_loudly():
         pool.shutdown()
 
 
+@pytest.mark.parametrize("how", ["explode1", "vanish1"])
+def test_dead_replica_is_taken_out_of_rotation(how):
+    """Replica 1 dies on its first request (with a 'fatal' message, or silently: EOF on its pipe). Its request
+    fails loudly, every later request is served by replica 0, and with no replica left generate() refuses at once
+    (it used to keep routing to the dead one and wait forever)."""
+    pool = ReplicaPool(how, EngineConfig(block_size=16), 2, worker=fake_replica_worker)
+    seen = []
+    pool.set_batch_size_observer(seen.append)
+    try:
+        async def one(rid, ids, n=2):
+            return [o async for o in pool.generate(ids, SamplingParams(max_tokens=n), rid)]
+
+        async def scenario():
+            first = await asyncio.gather(one("a", [1] * 70), one("b", [2] * 70), return_exceptions=True)
+            later = await asyncio.gather(*[one(f"c{i}", [3 + i] * 70) for i in range(4)])
+            return first, later
+        first, later = asyncio.run(scenario())
+        failed = [r for r in first if isinstance(r, Exception)]
+        served = [r for r in first if not isinstance(r, Exception)]
+        assert len(failed) == 1 and "replica 1 failed" in str(failed[0]) and len(served) == 1
+        assert all(outs[-1].finished and outs[-1].token_ids[0] // 1000 == 0 for outs in later)   # all on replica 0
+        assert pool.router.alive == [True, False] and pool.router.load == [0, 0]
+        assert seen and set(seen) == {1, 2}                     # llm_batch_size gets the replicas' step sizes
+        assert pool.stats()["kv_used_blocks"] >= 7
+        pool._replica_died(0, "test: the last one goes too")
+        with pytest.raises(RuntimeError, match="no engine replica is alive"):
+            asyncio.run(one("z", [9] * 70))
+    finally:
+        pool.shutdown()
+
+
 def _rank_main(rank, world, port, q):
     import torch.distributed as dist
 
