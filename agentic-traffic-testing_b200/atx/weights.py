@@ -28,6 +28,81 @@ def interleave_gate_up(gate: torch.Tensor, up: torch.Tensor) -> torch.Tensor:
     return torch.stack((gate.reshape(I // 64, 64, H), up.reshape(I // 64, 64, H)), dim=1).reshape(2 * I, H)
 
 
+class _DictSource:
+    def __init__(self, sd: Dict[str, torch.Tensor]):
+        self.sd = sd
+
+    def has(self, name: str) -> bool:
+        return name in self.sd
+
+    def shape(self, name: str):
+        return tuple(self.sd[name].shape)
+
+    def full(self, name: str) -> torch.Tensor:
+        return self.sd[name]
+
+    def rows(self, name: str, lo: int, hi: int) -> torch.Tensor:
+        return self.sd[name][lo:hi]
+
+    def cols(self, name: str, lo: int, hi: int) -> torch.Tensor:
+        return self.sd[name][:, lo:hi]
+
+
+class _SafetensorsSource:
+    """Name -> shard file from `model.safetensors.index.json` when the checkpoint has one (the sharded hub layout;
+    other *.safetensors files in the directory, e.g. Meta's `consolidated.*`, are then never opened), else from
+    the key lists of the `model*.safetensors` / `*.safetensors` files. Tensors are read as slices."""
+
+    def __init__(self, path: Path):
+        import json
+
+        from safetensors import safe_open
+
+        self._open = safe_open
+        self._handles: Dict[Path, object] = {}
+        self.where: Dict[str, Path] = {}
+        index = path / "model.safetensors.index.json"
+        if index.exists():
+            for name, fname in json.loads(index.read_text())["weight_map"].items():
+                self.where[name] = path / fname
+        else:
+            files = sorted(path.glob("model*.safetensors")) or sorted(
+                f for f in path.glob("*.safetensors") if not f.name.startswith("consolidated"))
+            if not files:
+                raise FileNotFoundError(f"no *.safetensors under {path}")
+            for f in files:
+                with safe_open(str(f), framework="pt", device="cpu") as sf:
+                    for k in sf.keys():
+                        self.where.setdefault(k, f)
+        self.bytes_read = 0
+
+    def _file(self, name: str):
+        f = self.where[name]
+        h = self._handles.get(f)
+        if h is None:
+            h = self._handles[f] = self._open(str(f), framework="pt", device="cpu").__enter__()
+        return h
+
+    def has(self, name: str) -> bool:
+        return name in self.where
+
+    def shape(self, name: str):
+        return tuple(self._file(name).get_slice(name).get_shape())
+
+    def _count(self, t: torch.Tensor) -> torch.Tensor:
+        self.bytes_read += t.numel() * t.element_size()
+        return t
+
+    def full(self, name: str) -> torch.Tensor:
+        return self._count(self._file(name).get_tensor(name))
+
+    def rows(self, name: str, lo: int, hi: int) -> torch.Tensor:
+        return self._count(self._file(name).get_slice(name)[lo:hi])
+
+    def cols(self, name: str, lo: int, hi: int) -> torch.Tensor:
+        return self._count(self._file(name).get_slice(name)[:, lo:hi])
+
+
 class LayerWeights:
     __slots__ = ("ln1", "wqkv", "wo", "ln2", "wgu", "wdown")
 
@@ -67,6 +142,12 @@ class ModelWeights:
         """`sd` uses HF names; values may be fp32/bf16 on any device. With tp_size > 1 only this rank's
         shard is kept (Megatron layout: q/k/v/gate/up split by output rows = heads / features, o/down by
         input columns, LM head by vocabulary rows; embedding and norms replicated)."""
+        return cls._from_source(cfg, _DictSource(sd), device, tp_size, tp_rank)
+
+    @classmethod
+    def _from_source(cls, cfg: ModelConfig, src, device: torch.device, tp_size: int, tp_rank: int) -> "ModelWeights":
+        """`src` answers full(name) / rows(name, lo, hi) / cols(name, lo, hi) / has(name): a state dict in memory, or
+        a checkpoint directory read slice by slice (a rank never touches bytes it does not keep)."""
         w = cls(cfg, device)
         w.tp_size, w.tp_rank = tp_size, tp_rank
         r, n = tp_rank, tp_size
@@ -74,30 +155,32 @@ class ModelWeights:
         def dev(t: torch.Tensor) -> torch.Tensor:
             return t.to(device=device, dtype=torch.bfloat16).contiguous()
 
-        def rows(t: torch.Tensor) -> torch.Tensor:   # output-feature (row) shard
-            k = t.shape[0] // n
-            return t[r * k:(r + 1) * k]
+        def rows(name: str) -> torch.Tensor:   # output-feature (row) shard
+            k = src.shape(name)[0] // n
+            return src.rows(name, r * k, (r + 1) * k)
 
-        def cols(t: torch.Tensor) -> torch.Tensor:   # input-feature (column) shard
-            k = t.shape[1] // n
-            return t[:, r * k:(r + 1) * k]
+        def cols(name: str) -> torch.Tensor:   # input-feature (column) shard
+            k = src.shape(name)[1] // n
+            return src.cols(name, r * k, (r + 1) * k)
 
-        w.embed = dev(sd["model.embed_tokens.weight"])
+        w.embed = dev(src.full("model.embed_tokens.weight"))
         for i in range(cfg.num_hidden_layers):
             p = f"model.layers.{i}."
             l = LayerWeights()
-            l.ln1 = dev(sd[p + "input_layernorm.weight"])
-            l.wqkv = dev(torch.cat([rows(sd[p + "self_attn.q_proj.weight"]), rows(sd[p + "self_attn.k_proj.weight"]),
-                                    rows(sd[p + "self_attn.v_proj.weight"])], dim=0))
-            l.wo = dev(cols(sd[p + "self_attn.o_proj.weight"]))
-            l.ln2 = dev(sd[p + "post_attention_layernorm.weight"])
-            l.wgu = dev(interleave_gate_up(rows(sd[p + "mlp.gate_proj.weight"]), rows(sd[p + "mlp.up_proj.weight"])))
-            l.wdown = dev(cols(sd[p + "mlp.down_proj.weight"]))
+            l.ln1 = dev(src.full(p + "input_layernorm.weight"))
+            l.wqkv = dev(torch.cat([rows(p + "self_attn.q_proj.weight"), rows(p + "self_attn.k_proj.weight"),
+                                    rows(p + "self_attn.v_proj.weight")], dim=0))
+            l.wo = dev(cols(p + "self_attn.o_proj.weight"))
+            l.ln2 = dev(src.full(p + "post_attention_layernorm.weight"))
+            l.wgu = dev(interleave_gate_up(rows(p + "mlp.gate_proj.weight"), rows(p + "mlp.up_proj.weight")))
+            l.wdown = dev(cols(p + "mlp.down_proj.weight"))
             w.layers.append(l)
-        w.norm = dev(sd["model.norm.weight"])
-        head = sd["model.embed_tokens.weight"] if cfg.tie_word_embeddings or "lm_head.weight" not in sd \
-            else sd["lm_head.weight"]
-        w.lm_head = w.embed if (n == 1 and head is sd["model.embed_tokens.weight"]) else dev(rows(head))
+        w.norm = dev(src.full("model.norm.weight"))
+        tied = cfg.tie_word_embeddings or not src.has("lm_head.weight")
+        if tied:
+            w.lm_head = w.embed if n == 1 else dev(rows("model.embed_tokens.weight"))
+        else:
+            w.lm_head = dev(rows("lm_head.weight"))
         w._check()
         return w
 
@@ -162,18 +245,10 @@ class ModelWeights:
     @classmethod
     def from_hf_dir(cls, cfg: ModelConfig, path: Path, device: torch.device, tp_size: int = 1,
                     tp_rank: int = 0) -> "ModelWeights":
-        """Load *.safetensors shards of an HF checkpoint directory (hub snapshot layout)."""
-        from safetensors import safe_open
-
-        files = sorted(Path(path).glob("*.safetensors"))
-        if not files:
-            raise FileNotFoundError(f"no *.safetensors under {path}")
-        sd: Dict[str, torch.Tensor] = {}
-        for f in files:
-            with safe_open(str(f), framework="pt", device="cpu") as sf:
-                for k in sf.keys():
-                    sd[k] = sf.get_tensor(k)
-        return cls.from_state_dict(cfg, sd, device, tp_size, tp_rank)
+        """Load an HF checkpoint directory (hub snapshot layout) tensor by tensor: each weight is read from its
+        safetensors shard as the slice this rank keeps and moved to the device at once, so host memory holds one
+        tensor at a time — a 70B checkpoint under TP=8 costs each rank 1/8 of the bytes, not 8 x 141 GB."""
+        return cls._from_source(cfg, _SafetensorsSource(Path(path)), device, tp_size, tp_rank)
 
     def _check(self) -> None:
         c, n = self.cfg, self.tp_size

@@ -73,6 +73,44 @@ def test_hf_checkpoint_directory_round_trip(tmp_path, tie):
             assert torch.equal(ls.wdown, lf.wdown[:, r * (m.intermediate_size // n):(r + 1) * (m.intermediate_size // n)])
 
 
+def test_sharded_checkpoint_is_read_slice_by_slice_and_decoys_are_ignored(tmp_path):
+    """The hub layout of the large models: several model-0000x-of-0000N.safetensors shards + model.safetensors.index.json,
+    often with Meta's `consolidated.*.safetensors` next to them. A tensor-parallel rank reads only the slices it
+    keeps (host memory: one tensor at a time; it used to read every shard whole on every rank) and never opens a
+    file the index does not name."""
+    from safetensors.torch import save_file
+
+    from atx.weights import _SafetensorsSource
+
+    d, model = _write_checkpoint(tmp_path, False)
+    sd = {k: v.contiguous() for k, v in model.state_dict().items()}
+    (d / "model.safetensors").unlink()
+    names = sorted(sd)
+    parts = [names[0::3], names[1::3], names[2::3]]
+    wmap = {}
+    for i, part in enumerate(parts):
+        fname = f"model-{i + 1:05d}-of-00003.safetensors"
+        save_file({k: sd[k] for k in part}, str(d / fname))
+        wmap.update({k: fname for k in part})
+    (d / "model.safetensors.index.json").write_text(json.dumps({"metadata": {}, "weight_map": wmap}))
+    (d / "consolidated.00.safetensors").write_bytes(b"not a safetensors file at all")     # must never be opened
+    m = resolve_model(str(d)).config
+    dev = torch.device("cpu")
+    full = ModelWeights.from_hf_dir(m, d, dev)
+    assert torch.equal(full.layers[1].wdown, sd["model.layers.1.mlp.down_proj.weight"])
+    total = sum(v.numel() * 2 for v in sd.values())
+    replicated = sum(v.numel() * 2 for k, v in sd.items() if "norm" in k or "embed" in k)
+    for r in range(2):
+        src = _SafetensorsSource(d)
+        s = ModelWeights._from_source(m, src, dev, 2, r)
+        assert src.bytes_read == replicated + (total - replicated) // 2     # its shard and nothing else
+        assert torch.equal(s.layers[0].wo, full.layers[0].wo[:, r * (m.q_size // 2):(r + 1) * (m.q_size // 2)])
+    # without an index the model*.safetensors files are scanned; the decoy still is not touched
+    (d / "model.safetensors.index.json").unlink()
+    again = ModelWeights.from_hf_dir(m, d, dev)
+    assert torch.equal(again.layers[1].wgu, full.layers[1].wgu)
+
+
 def test_missing_checkpoint_is_a_loud_error(tmp_path, monkeypatch):
     monkeypatch.delenv("LLM_RANDOM_INIT_SEED", raising=False)
     monkeypatch.setenv("HF_HUB_OFFLINE", "1")
