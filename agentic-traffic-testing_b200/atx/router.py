@@ -25,7 +25,10 @@ from .kv_cache import block_hash
 from .scheduler import SamplingParams
 
 AFFINITY_BLOCKS = 4          # prompt blocks hashed for affinity (64 tokens at block_size 16)
-SPILL_FACTOR = 2.0           # leave the preferred replica when it holds this many times the lightest load
+SPILL_FACTOR = 2.0           # leave the preferred replica when it holds this many times the lightest load ...
+SPILL_SLACK = 8192           # ... plus this many outstanding tokens: one fan-out burst (6 x ~1.3k) stays together even
+#                              when other replicas are idle (its requests share a prefix and decode in one batch at
+#                              the cost of one), the NEXT burst goes to the lightest replica
 
 
 def _engine_worker(rank: int, model: str, ecfg: EngineConfig, req, resp) -> None:
@@ -104,7 +107,7 @@ class Router:
         choice = lightest
         if key is not None:
             home = self._home.get(key)
-            if home is not None and self.alive[home] and self.load[home] <= SPILL_FACTOR * self.load[lightest] + cost:
+            if home is not None and self.alive[home] and self.load[home] <= SPILL_FACTOR * self.load[lightest] + max(cost, SPILL_SLACK):
                 choice = home
             self._home[key] = choice
             if len(self._home) > 65536:

@@ -30,8 +30,32 @@ sys.path.insert(0, str(ROOT / "agentic-traffic-testing_b200"))
 sys.path.insert(0, str(ROOT))
 os.environ.setdefault("LLM_OTEL_EXPORT", "0")
 os.environ.setdefault("LLM_IGNORE_EOS", "1")
-if os.environ.get("ATX_KEEP_NCCL_DEBUG") != "1":
-    os.environ["NCCL_DEBUG"] = "WARN"  # NCCL prints its version banner on stdout otherwise; stdout carries one JSON line
+# NCCL's own log stays on (the driver counts the ranks of each communicator from it) without touching stdout, which
+# carries the one JSON line: every process logs to a file of its own and replays the communicator lines on stderr
+# when it exits. (Pointing NCCL at /dev/stderr re-opens and truncates whatever file stderr was redirected to.)
+os.environ.setdefault("NCCL_DEBUG", "INFO")
+os.environ.setdefault("NCCL_DEBUG_SUBSYS", "INIT")
+if "NCCL_DEBUG_FILE" not in os.environ and os.environ["NCCL_DEBUG"].upper() not in ("WARN", "VERSION"):
+    import atexit
+    import glob
+    import tempfile
+
+    _nccl_dir = os.environ.setdefault("ATX_NCCL_LOG_DIR", tempfile.mkdtemp(prefix="atx_nccl_"))
+    os.environ["NCCL_DEBUG_FILE"] = os.path.join(_nccl_dir, "nccl.%h.%p.log")
+
+    def _replay_nccl_log(pid=os.getpid()):
+        if os.getpid() != pid:        # forked / spawned children inherit the hook's environment, not this process's log
+            return
+        for path in glob.glob(os.path.join(_nccl_dir, f"nccl.*.{pid}.log")):
+            try:
+                with open(path, errors="replace") as f:
+                    for line in f:
+                        if "nranks" in line or "Init COMPLETE" in line or "NCCL version" in line:
+                            sys.stderr.write(line)
+            except OSError:
+                pass
+        sys.stderr.flush()
+    atexit.register(_replay_nccl_log)
 
 METRIC = "Llama-3.1-8B decode tokens/s + p50 TTFT under agent fan-out"
 UNIT = "tokens/s"
@@ -142,8 +166,9 @@ def run_burst(engine, prompts):
     return seqs
 
 
-async def http_bursts(app, steps, first_step, record):
-    """K bursts through POST /chat on a real localhost socket, 6 concurrent clients per burst."""
+async def http_bursts(app, steps, first_step, record, bursts_per_step: int = 1):
+    """K steps through POST /chat on a real localhost socket, 6 concurrent clients per burst (and, behind a
+    front door over several replicas, `bursts_per_step` bursts arriving together)."""
     import aiohttp
     from aiohttp import web
 
@@ -160,7 +185,8 @@ async def http_bursts(app, steps, first_step, record):
                 assert r.status == 200, body
                 return body["meta"]
         for k in range(steps):
-            metas = await asyncio.gather(*[one(t) for t in burst_texts(first_step + k)])
+            texts = [t for j in range(bursts_per_step) for t in burst_texts((first_step + k) * bursts_per_step + j)]
+            metas = await asyncio.gather(*[one(t) for t in texts])
             record(metas)
     await runner.cleanup()
 
@@ -328,6 +354,140 @@ def cpu_config1(threads: int) -> dict:
             "host_dram_gbs": round(wbytes / 1e9 * 63 / dec, 1)}
 
 
+def tp70b_measure(dist, rank, world, local, pk, steps, warmup, out_tokens=256, layers=None, prefetch_ab=""):
+    """BASELINE.json configs[3]: Llama-3.1-70B sharded tensor-parallel over the `world` GPUs of the box (one rank
+    per GPU, schedulers in lockstep), agent fan-out batch 32. Returns the record (value = output tokens/s)."""
+    import numpy as np
+    import torch
+
+    from atx.config import EngineConfig, ModelSource, model_config_by_name
+    from atx.engine import LLMEngine
+    from atx.scheduler import SamplingParams
+
+    mcfg = model_config_by_name("70b", layers)
+    B, P, O = 32, 1024, out_tokens
+    ecfg = EngineConfig(max_model_len=4096, max_num_seqs=B, max_num_batched_tokens=8192, gpu_memory_utilization=0.90,
+                        device=local, tp_size=world, tp_rank=rank)
+    engine = LLMEngine(ModelSource(mcfg, None, 0), ecfg)
+    r = engine.runner
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def one(step):
+        rng = np.random.default_rng(4 + step)     # identical on every rank: schedulers run in lockstep
+        shared = rng.integers(0, 128000, SHARED).tolist()
+        prompts = [shared + rng.integers(0, 128000, P - SHARED).tolist() for _ in range(B)]
+        params = SamplingParams(temperature=0.0, max_tokens=O, ignore_eos=True)
+        r.step_events = []
+        seqs = [engine.add_request(f"t{step}-{i}", p, params) for i, p in enumerate(prompts)]
+        t = time.monotonic()
+        for s_ in seqs:
+            s_.arrival = t
+        while engine.has_work():
+            engine.step()
+        ev, r.step_events = r.step_events, None
+        return seqs, ev
+    for w in range(warmup):
+        one(1000 + w)
+    barrier()
+    l0 = r.kernel_launches
+    t0 = time.perf_counter()
+    evs, ttfts = [], []
+    for k in range(steps):
+        seqs, ev = one(k)
+        evs += ev
+        ttfts += [s.first_token_time - s.arrival for s in seqs]
+    barrier()
+    wall = max_over_ranks(dist, [time.perf_counter() - t0], "cuda")[0]
+    dec = [(a.elapsed_time(b), ctx) for (a, b, nd, npf, ctx) in evs if npf == 0 and nd == B]
+    ms = max_over_ranks(dist, [sum(d[0] for d in dec) / len(dec)], "cuda")[0]
+    out = {}
+    # optional A/B inside the same process (an 8-GPU box is expensive to bring up twice): decode step time
+    # with the post-all-reduce GEMMs prefetching `kb` weight slices into L2 while they wait
+    ab = {}
+    for kb in [int(v) for v in prefetch_ab.split(",") if v.strip()]:
+        r.tp_l2_prefetch_kb = kb
+        r.close()                      # drop the captured graphs: they bake the flag in
+        one(2000 + kb)
+        _, ev2 = one(3000 + kb)
+        d2 = [a.elapsed_time(b) for (a, b, nd, npf, ctx) in ev2 if npf == 0 and nd == B]
+        ab[str(kb)] = round(max_over_ranks(dist, [sum(d2) / len(d2)], "cuda")[0], 3)
+    if ab:
+        out["tp_l2_prefetch_ab_decode_step_ms"] = ab
+    byts = (mcfg.weight_bytes_per_decode_step() + mcfg.kv_bytes_per_token() * (sum(d[1] for d in dec) / len(dec))) / world
+    mode = ("ll: push protocol, data is the flag (atx_allreduce_add_rmsnorm_ll)" if r.ll_ar else
+            "sharded: flag barrier + reduce-scatter/all-gather kernel" if r.sharded_ar else
+            "fused: flag barrier + one-shot kernel" if r.fused_ar else "nccl")
+    out.update({"metric": "Llama-3.1-70B tensor-parallel decode tokens/s + p50 TTFT under agent fan-out",
+                "value": round(steps * B * O / wall, 1), "unit": UNIT, "steps": steps, "warmup": warmup,
+                "ms_per_step": round(1e3 * wall / steps, 1),
+                "scaling": "strong", "ttft_p50_ms": round(1e3 * statistics.median(ttfts), 1),
+                "decode_step": {"ms": round(ms, 3), "algorithmic_bytes_per_gpu": round(byts),
+                                "achieved": round(byts / ms / 1e6, 1), "peak": pk["hbm_gbs"], "unit": "GB/s per GPU",
+                                "frac": round(byts / ms / 1e6 / pk["hbm_gbs"], 4),
+                                "decode_tokens_per_s": round(B / ms * 1e3, 1),
+                                "allreduces_per_step": 2 * mcfg.num_hidden_layers + 1,
+                                "allreduce_message_bytes": B * mcfg.hidden_size * 4},
+                "gpu_launches": r.kernel_launches - l0,
+                "tp_allreduce": mode,
+                "config": {"workload": f"BASELINE configs[3]: Llama-3.1-70B ({mcfg.num_hidden_layers} layers) tensor-"
+                                       f"parallel TP={world} over NVLink, agent fan-out batch {B}, {P}-token prompts "
+                                       f"(768 shared), {O} greedy tokens; decode-sized steps: all-reduce + residual add + "
+                                       f"RMSNorm in one kernel of ours over peer memory (mode: {mode.split(':')[0]}), "
+                                       "replayed as CUDA graphs; prefill-sized steps and the logits: NCCL",
+                           "parallelism": f"tp{world}"}})
+    engine.runner.close()
+    del engine, r
+    import gc
+
+    gc.collect()
+    torch.cuda.empty_cache()
+    return out
+
+
+def routed_dp_measure(world: int, steps: int, ecfg, model: str = "random:8b:0") -> dict:
+    """The 8B replicas behind ONE front door (north_star "one data-parallel replica per GPU behind the
+    scheduler"): this process serves POST /chat on one port and routes over `world` engine processes, one per GPU
+    (atx/router.py:ReplicaPool — prefix affinity, then least outstanding tokens); each step is `world` fan-out
+    bursts arriving together (the per-GPU work of the independent-rank measurement). Wall clock, host text in /
+    text out."""
+    import contextlib
+    import dataclasses
+    import io
+
+    from atx.router import ReplicaPool
+    from llm import serve_llm as S
+    from llm.backend import B200Backend
+
+    t0 = time.perf_counter()
+    pool = ReplicaPool(model, dataclasses.replace(ecfg, device=0), world)
+    start_s = time.perf_counter() - t0
+    S._backend = B200Backend(model, ecfg.max_model_len, None, ecfg.max_num_seqs, ecfg.max_num_batched_tokens,
+                             ecfg.gpu_memory_utilization, tracer=S._tracer, engine=pool)
+    metas = []
+    try:
+        with contextlib.redirect_stdout(io.StringIO()):
+            asyncio.run(http_bursts(S.create_app(), 3, 30_000, lambda m: None, world))   # graphs, HTTP path warm
+            tw = time.perf_counter()
+            asyncio.run(http_bursts(S.create_app(), steps, 40_000, metas.append, world))
+            wall = time.perf_counter() - tw
+        loads = list(pool.router.load)
+    finally:
+        S._backend = None
+        pool.shutdown()
+    flat = [m for burst in metas for m in burst]
+    assert all(m["completion_tokens"] == OUT and m["prompt_tokens"] == PROMPT - 1 for m in flat)
+    return {"value": round(len(flat) * OUT / wall, 1), "unit": UNIT, "ms_per_step": round(1e3 * wall / steps, 2),
+            "ttft_p50_ms": round(1e3 * statistics.median(m["queue_wait_s"] for m in flat), 2),
+            "requests": len(flat), "replicas": world, "replica_start_s": round(start_s, 1),
+            "outstanding_tokens_after": loads,
+            "path": f"HTTP POST /chat on 127.0.0.1, ONE aiohttp front door -> ReplicaPool router -> {world} engine "
+                    f"processes (one per GPU) over pipes; {world} bursts x 6 requests arrive together per step"}
+
+
 # ------------------------------------------------------------------------------------------------------
 def run_other_workload(args, rank, world, local):
     """BASELINE.json configs[2..4]: opt-in workloads (`--workload trace|long|tp70b`). Each prints one JSON
@@ -442,74 +602,13 @@ def run_other_workload(args, rank, world, local):
                                            f"(chunked prefill, 8192-token budget) + {O} greedy tokens over paged KV",
                                "parallelism": "1 GPU", "kv_blocks": r.num_blocks}})
     elif args.workload == "tp70b":
-        mcfg = model_config_by_name("70b", args.layers)
-        B, P, O = 32, 1024, args.tp_out
-        ecfg = EngineConfig(max_model_len=4096, max_num_seqs=B, max_num_batched_tokens=8192, gpu_memory_utilization=0.90,
-                            device=local, tp_size=world, tp_rank=rank)
-        engine = LLMEngine(ModelSource(mcfg, None, 0), ecfg)
-        r = engine.runner
-        import numpy as np
-
-        def one(step):
-            rng = np.random.default_rng(4 + step)     # identical on every rank: schedulers run in lockstep
-            shared = rng.integers(0, 128000, SHARED).tolist()
-            prompts = [shared + rng.integers(0, 128000, P - SHARED).tolist() for _ in range(B)]
-            params = SamplingParams(temperature=0.0, max_tokens=O, ignore_eos=True)
-            r.step_events = []
-            seqs = [engine.add_request(f"t{step}-{i}", p, params) for i, p in enumerate(prompts)]
-            t = time.monotonic()
-            for s_ in seqs:
-                s_.arrival = t
-            while engine.has_work():
-                engine.step()
-            ev, r.step_events = r.step_events, None
-            return seqs, ev
-        for w in range(args.warmup):
-            one(1000 + w)
-        barrier()
-        t0 = time.perf_counter()
-        evs, ttfts = [], []
-        for k in range(args.steps):
-            seqs, ev = one(k)
-            evs += ev
-            ttfts += [s.first_token_time - s.arrival for s in seqs]
-        barrier()
-        wall = max_over_ranks(dist, [time.perf_counter() - t0], "cuda")[0]
-        dec = [(a.elapsed_time(b), ctx) for (a, b, nd, npf, ctx) in evs if npf == 0 and nd == B]
-        ms = sum(d[0] for d in dec) / len(dec)
-        # optional A/B inside the same process (an 8-GPU box is expensive to bring up twice): decode step time
-        # with the post-all-reduce GEMMs prefetching `kb` weight slices into L2 while they wait
-        ab = {}
-        for kb in [int(v) for v in args.tp_prefetch_ab.split(",") if v.strip()]:
-            r.tp_l2_prefetch_kb = kb
-            r.close()                      # drop the captured graphs: they bake the flag in
-            one(2000 + kb)
-            _, ev2 = one(3000 + kb)
-            d2 = [a.elapsed_time(b) for (a, b, nd, npf, ctx) in ev2 if npf == 0 and nd == B]
-            ab[str(kb)] = round(max_over_ranks(dist, [sum(d2) / len(d2)], "cuda")[0], 3)
-        if ab:
-            out["tp_l2_prefetch_ab_decode_step_ms"] = ab
-        byts = (mcfg.weight_bytes_per_decode_step() + mcfg.kv_bytes_per_token() * (sum(d[1] for d in dec) / len(dec))) / world
-        out.update({"metric": "Llama-3.1-70B tensor-parallel decode tokens/s + p50 TTFT under agent fan-out",
-                    "value": round(args.steps * B * O / wall, 1), "ms_per_step": round(1e3 * wall / args.steps, 1),
-                    "scaling": "strong", "ttft_p50_ms": round(1e3 * statistics.median(ttfts), 1),
-                    "decode_step": {"ms": round(ms, 3), "algorithmic_bytes_per_gpu": round(byts),
-                                    "achieved": round(byts / ms / 1e6, 1), "peak": pk["hbm_gbs"], "unit": "GB/s per GPU",
-                                    "frac": round(byts / ms / 1e6 / pk["hbm_gbs"], 4),
-                                    "decode_tokens_per_s": round(B / ms * 1e3, 1),
-                                    "allreduces_per_step": 2 * mcfg.num_hidden_layers + 1,
-                                    "allreduce_message_bytes": B * mcfg.hidden_size * 4},
-                    "gpu_launches": r.kernel_launches,
-                    "tp_allreduce": ("ll: push protocol, data is the flag (atx_allreduce_add_rmsnorm_ll)" if r.ll_ar else
-                                     "sharded: flag barrier + reduce-scatter/all-gather kernel" if r.sharded_ar else
-                                     "fused: flag barrier + one-shot kernel" if r.fused_ar else "nccl"),
-                    "config": {"workload": f"BASELINE configs[3]: Llama-3.1-70B ({mcfg.num_hidden_layers} layers) tensor-"
-                                           f"parallel TP={world} over NVLink, agent fan-out batch {B}, {P}-token prompts "
-                                           f"(768 shared), {O} greedy tokens; the per-layer all-reduce is fused with the "
-                                           "residual add and RMSNorm in our own kernel for decode-sized steps (see "
-                                           "tp_allreduce), NCCL for prefill-sized steps and the logits; decode steps "
-                                           "replayed as CUDA graphs",
-                               "parallelism": f"tp{world}"}})
+        out.update(tp70b_measure(dist, rank, world, local, pk, args.steps, args.warmup, args.tp_out, args.layers,
+                                 args.tp_prefetch_ab))
+        if rank == 0:
+            print(json.dumps(out), flush=True)
+        if dist is not None:
+            dist.destroy_process_group()
+        return
     if rank == 0:
         print(json.dumps(out), flush=True)
     engine.runner.close()
@@ -527,6 +626,9 @@ def main() -> None:
     ap.add_argument("--no-prefix-cache", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-multi", action="store_true", help="N > 1: skip the routed-DP and 70B-TP records")
+    ap.add_argument("--tp70b-any-n", action="store_true", help="attach the 70B tensor-parallel record at any N > 1 "
+                                                               "(default: only at N = 8, BASELINE configs[3])")
     ap.add_argument("--workload", default="fanout", choices=["fanout", "trace", "long", "tp70b"],
                     help="fanout = headline BASELINE configs[1] (default); the others are configs[2..4]")
     ap.add_argument("--trace-out", default="", help="directory for response.json / llm_calls.jsonl of a trace replay")
@@ -589,10 +691,12 @@ def main() -> None:
 
     torch.cuda.set_device(local)
     dist = None
+    host_pg = None
     if world > 1:
         import torch.distributed as dist
 
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        host_pg = dist.new_group(backend="gloo")   # host-side waits that must not occupy a GPU (routed phase)
     mcfg = model_config_by_name(args.model)
     ecfg = EngineConfig(max_model_len=4096, max_num_seqs=12, max_num_batched_tokens=8192,
                         gpu_memory_utilization=0.90, enable_prefix_caching=not args.no_prefix_cache, device=local)
@@ -683,6 +787,45 @@ def main() -> None:
                "ttft_p50_ms": round(1e3 * statistics.median(e2e_ttft), 2),
                "path": "HTTP POST /chat on 127.0.0.1 (aiohttp server + client), text prompts, byte tokenizer"}
 
+    # ---- N > 1: the two multi-GPU rows of SURVEY 8e measured in the same launch ------------------------
+    tp70b = routed = None
+    pdl_on, kv_blocks = bool(r.flags), r.num_blocks
+    if world > 1 and not args.no_multi:
+        import gc
+
+        from llm import serve_llm as S_
+
+        S_._backend = None
+        r.close()
+        aeng = engine = r = None           # noqa: F841  (drop every reference: 16 GB of weights + the KV pool)
+        gc.collect()
+        torch.cuda.empty_cache()
+        barrier()
+        if world == 8 or args.tp70b_any_n:
+            # configs[3]: the only path with a collective. Same processes, same NCCL communicator.
+            try:
+                tp70b = tp70b_measure(dist, rank, world, local, pk, max(1, min(args.steps, 3)), 1, 256)
+            except Exception as exc:       # every rank fails alike (lockstep); keep the DP line
+                tp70b = {"failed": f"{type(exc).__name__}: {exc}"}
+            barrier()
+        dist.barrier(group=host_pg)
+        if rank == 0:
+            try:
+                routed = routed_dp_measure(world, args.steps, ecfg, "random:%s:0" % args.model)
+            except Exception as exc:
+                routed = {"failed": f"{type(exc).__name__}: {exc}"}
+        dist.barrier(group=host_pg)        # ranks 1..N-1 wait on the host: their GPUs belong to the replicas now
+        if routed is not None and "value" in routed:
+            # the N-GPU end-to-end number is the one with the front door in the path; the per-rank HTTP arm
+            # (every rank its own server and clients) stays beside it
+            e2e_indep, e2e = e2e, {
+                "value": routed["value"], "unit": UNIT,
+                "h2d_bytes_per_step": (e2e or {}).get("h2d_bytes_per_step", 0) * world,
+                "d2h_bytes_per_step": (e2e or {}).get("d2h_bytes_per_step", 0) * world,
+                "ttft_p50_ms": routed["ttft_p50_ms"], "path": routed["path"],
+                "bytes_note": "staging bytes per replica as counted in the independent-rank arm, times the replicas"}
+            routed["independent_ranks_e2e"] = e2e_indep
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
@@ -703,17 +846,19 @@ def main() -> None:
             "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": WORKLOAD_TEXT,
                        "parallelism": f"dp{world} (independent replicas, no collective)",
-                       "prefix_cache": not args.no_prefix_cache, "cuda_graphs": True, "pdl": bool(r.flags),
+                       "prefix_cache": not args.no_prefix_cache, "cuda_graphs": True, "pdl": pdl_on,
                        "l2": "inputs larger than L2: 15 GB of weights streamed per decode step vs 126 MB L2",
                        "max_num_seqs": ecfg.max_num_seqs, "max_num_batched_tokens": ecfg.max_num_batched_tokens,
-                       "kv_blocks": r.num_blocks},
+                       "kv_blocks": kv_blocks},
             "ttft_p50_ms": round(1e3 * statistics.median(ttfts), 2),
             "ttft_max_ms": round(1e3 * max(ttfts), 2),
             "host_ms_per_step": round(host_ms / args.steps, 3),
             "gpu_launches": launches, "engine_steps": eng_steps,
             "clocks": clocks, "roofline": roof, "decode_step": decode_step, "prefill": prefill, "e2e": e2e,
             "cpu_baseline": cpu,
-        }))
+            **({"routed_dp": routed} if routed is not None else {}),
+            **({"tp70b": tp70b} if tp70b is not None else {}),
+        }), flush=True)
     if dist is not None:
         dist.destroy_process_group()
 

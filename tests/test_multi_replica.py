@@ -26,9 +26,18 @@ def test_router_policy_prefix_affinity_then_least_loaded():
     assert d not in (a, c)
     for _ in range(20):                             # the home replica spills once it is clearly busier
         last = r.pick(shared + [4], 1000)
-    assert last != a or r.load[a] <= 2.0 * min(r.load) + 1000
+    assert last != a or r.load[a] <= 2.0 * min(r.load) + 8192
+    assert max(r.load) <= 2.0 * min(r.load) + 8192 + 1000
     r.done(a, 100)
     assert all(x >= 0 for x in r.load)
+    # N fan-out bursts arriving interleaved at N idle replicas: every burst stays together on its own replica
+    r = Router(4, 16)
+    bursts = [[100 * b + i for i in range(64)] for b in range(4)]
+    where = {b: set() for b in range(4)}
+    for i in range(6):
+        for b in range(4):
+            where[b].add(r.pick(bursts[b] + [i] * 200, 1280))
+    assert all(len(v) == 1 for v in where.values()) and len({next(iter(v)) for v in where.values()}) == 4
 
 
 def test_replica_pool_streams_routes_and_reports_errors():
