@@ -24,7 +24,7 @@ FLAG_PDL = 1
 EXPORTS = [
     "atx_last_error", "atx_version", "atx_device_info",
     "atx_gemm_plan_create", "atx_gemm_plan_destroy", "atx_gemm_run", "atx_gemm_auto_splits",
-    "atx_gemm_set_l2_prefetch", "atx_gemm_qkv_rope_kv",
+    "atx_gemm_set_l2_prefetch",
     "atx_embed_gather", "atx_rmsnorm", "atx_rope_kv_write", "atx_silu_mul", "atx_allreduce_add_rmsnorm",
     "atx_reduce_scatter_rmsnorm_all_gather", "atx_allreduce_add_rmsnorm_ll",
     "atx_paged_attn_decode_workspace_bytes", "atx_paged_attn_decode", "atx_paged_attn_prefill",
@@ -72,7 +72,6 @@ def load() -> C.CDLL:
     lib.atx_gemm_auto_splits.argtypes = [i64, i64, i32]
     lib.atx_gemm_set_l2_prefetch.argtypes = [i32]
     lib.atx_gemm_set_l2_prefetch.restype = None
-    lib.atx_gemm_qkv_rope_kv.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp]
     lib.atx_embed_gather.argtypes = [vp, vp, vp, i32, i32, i32, vp]
     lib.atx_rmsnorm.argtypes = [vp, vp, vp, vp, vp, i32, i32, f32, vp, i64, i32, vp]
     lib.atx_allreduce_add_rmsnorm.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), vp, i32, vp, i32, i32, vp, vp, vp, i32,
@@ -180,17 +179,6 @@ def rope_kv_write(qkv: torch.Tensor, positions: torch.Tensor, slots: torch.Tenso
     _check(load().atx_rope_kv_write(qkv.data_ptr(), positions.data_ptr(), slots.data_ptr(), cos_sin.data_ptr(),
                                     q_out.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(), T, Hq, Hkv, D,
                                     block_size, flags, _stream()))
-
-
-def gemm_qkv_rope_kv(plan: "GemmPlan", T: int, positions: torch.Tensor, slots: torch.Tensor, cos_sin: torch.Tensor,
-                     q_out: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, Hq: int, Hkv: int, D: int,
-                     block_size: int, splits: int = 0, flags: int = 0) -> None:
-    _dev(positions, slots, cos_sin, q_out, k_cache, v_cache)
-    assert positions.dtype == torch.int32 and slots.dtype == torch.int32 and cos_sin.dtype == torch.float32
-    assert q_out.dtype == torch.bfloat16 and k_cache.dtype == torch.bfloat16 and v_cache.dtype == torch.bfloat16
-    _check(load().atx_gemm_qkv_rope_kv(plan._h, T, positions.data_ptr(), slots.data_ptr(), cos_sin.data_ptr(),
-                                       q_out.data_ptr(), k_cache.data_ptr(), v_cache.data_ptr(), Hq, Hkv, D, block_size,
-                                       splits, flags, _stream()))
 
 
 def silu_mul(gu: torch.Tensor, act: torch.Tensor, T: int, I: int, flags: int = 0) -> None:

@@ -57,6 +57,9 @@ class ModelRunner:
         self.Tmax = max(16, e.max_num_batched_tokens)
         self.Smax = max(1, e.max_num_seqs)
         self.bs = e.block_size
+        if self.bs <= 0 or self.bs % 16:
+            raise ValueError(f"block_size={self.bs}: KV pages hold a multiple of 16 tokens (vLLM's default 16; "
+                             "the attention kernels stage whole 16-token tiles)")
         self.MB = (e.max_model_len + self.bs - 1) // self.bs
         self.tp, self.tp_rank, self.tp_group = max(1, e.tp_size), e.tp_rank, None
         tp = self.tp
@@ -171,12 +174,6 @@ class ModelRunner:
         self.flags = _cabi.FLAG_PDL if e.use_pdl else 0
         self.lib.atx_gemm_set_l2_prefetch(int(os.environ.get("ATX_L2_PREFETCH_KB", "0")))
         self.tp_l2_prefetch_kb = int(os.environ.get("ATX_TP_L2_PREFETCH_KB", "0"))
-        # RoPE + KV write in the qkv GEMM's epilogue (atx_gemm_qkv_rope_kv): correct, but measured SLOWER than
-        # split-K atomics + the separate RoPE kernel (8B decode step 2.96 vs 2.85 ms; 70B/TP8 shard 5.93 vs 5.03 ms):
-        # the cluster barrier + DSMEM reduction on the tail of every tile costs more than the launch it saves
-        self.fuse_qkv_rope = os.environ.get("ATX_FUSE_QKV_ROPE", "0") == "1"
-        self.qkv_splits = int(os.environ.get("ATX_QKV_SPLITS", "0"))   # 0 = let the library choose
-
         self.scale = float(m.head_dim) ** -0.5
         self.launches_last_step = 0
         self.kernel_launches = 0  # cumulative count of our kernels launched (graph replays included)
@@ -257,26 +254,20 @@ class ModelRunner:
         ck(lib.atx_embed_gather(dp["ids"], w.embed.data_ptr(), h, T, H, V, st))
         n += 1
         sp_qkv = lib.atx_gemm_auto_splits(qkv_size, H, T)
-        fuse_rope = D == 128 and T <= 64 and self.fuse_qkv_rope
         qb = q_size * 2  # bytes per row of q / attn
         for li, l in enumerate(w.layers):
             p_qkv, p_o, p_gu, p_down = self.plans[li]
             kc, vc = self.k_cache[li].data_ptr(), self.v_cache[li].data_ptr()
-            if fuse_rope:    # decode-sized step, head_dim 128: RoPE + KV write in the qkv GEMM's epilogue
-                norm(l.ln1.data_ptr(), xn)
-                ck(lib.atx_gemm_qkv_rope_kv(p_qkv._h, T, dp["pos"], dp["slots"], self.rope.data_ptr(), q, kc, vc, Hq,
-                                            Hkv, D, self.bs, self.qkv_splits, fl_ar, st))
-                n += 1
+            if sp_qkv > 1:   # split-K accumulates into qkv: the norm kernel's spare CTAs clear it
+                norm(l.ln1.data_ptr(), xn, qkv, T * qkv_size * 4)
+                ck(lib.atx_gemm_run(p_qkv._h, qkv, qkv_size, T, _cabi.GEMM_ADD_F32, sp_qkv, fl_ar, st))
             else:
-                if sp_qkv > 1:   # split-K accumulates into qkv: the norm kernel's spare CTAs clear it
-                    norm(l.ln1.data_ptr(), xn, qkv, T * qkv_size * 4)
-                    ck(lib.atx_gemm_run(p_qkv._h, qkv, qkv_size, T, _cabi.GEMM_ADD_F32, sp_qkv, fl_ar, st))
-                else:
-                    norm(l.ln1.data_ptr(), xn)
-                    ck(lib.atx_gemm_run(p_qkv._h, qkv, qkv_size, T, _cabi.GEMM_STORE_F32, 1, fl_ar, st))
-                ck(lib.atx_rope_kv_write(qkv, dp["pos"], dp["slots"], self.rope.data_ptr(), q, kc, vc, T, Hq, Hkv, D,
-                                         self.bs, fl, st))
-                n += 2
+                norm(l.ln1.data_ptr(), xn)
+                ck(lib.atx_gemm_run(p_qkv._h, qkv, qkv_size, T, _cabi.GEMM_STORE_F32, 1, fl_ar, st))
+            n += 1
+            ck(lib.atx_rope_kv_write(qkv, dp["pos"], dp["slots"], self.rope.data_ptr(), q, kc, vc, T, Hq, Hkv, D,
+                                     self.bs, fl, st))
+            n += 1
             if n_dec:
                 ck(lib.atx_paged_attn_decode(q, kc, vc, dp["dec_bt"], dp["dec_lens"], attn, self.ws.data_ptr(),
                                              self.ws.numel() * 4, n_dec, Hq, Hkv, D, self.bs, self.MB, dec_splits,

@@ -282,12 +282,6 @@ int launch_prefill_tc(const void* q, const void* kc, const void* vc, const int* 
 
 using namespace atx;
 
-// ATX_PREFILL_TC=0 keeps the mma.sync kernel for head_dim 128 as well
-static const bool g_prefill_tc = [] {
-    const char* e = getenv("ATX_PREFILL_TC");
-    return !(e && e[0] == '0');
-}();
-
 extern "C" {
 
 int atx_paged_attn_prefill(const void* q, const void* k_cache, const void* v_cache, const int* block_table,
@@ -303,7 +297,7 @@ int atx_paged_attn_prefill(const void* q, const void* k_cache, const void* v_cac
                 max_q_len, Hq, Hkv, block_size, max_blocks);
     ATX_REQUIRE(total_q >= max_q_len && num_blocks > 0, "atx_paged_attn_prefill: total_q=%lld / num_blocks=%lld", total_q,
                 num_blocks);
-    if (D == 128 && block_size == 16 && g_prefill_tc && (reinterpret_cast<uintptr_t>(q) & 15) == 0)
+    if (D == 128 && block_size == 16 && (reinterpret_cast<uintptr_t>(q) & 15) == 0)   // the tcgen05 kernel
         return launch_prefill_tc(q, k_cache, v_cache, block_table, cu_q, ctx_lens, out, S, max_q_len, total_q, num_blocks,
                                  Hq, Hkv, max_blocks, scale, flags, stream);
     if (D == 128)

@@ -1,20 +1,25 @@
 // Causal prefill attention over the paged KV cache on tcgen05 tensor cores (head_dim 128, 16-token pages).
 //
-// Same arithmetic as attn_prefill.cu (transformers modeling_llama.py:199-222, fp32 softmax :217). The
-// mma.sync version tops out at 42 % of the LEGACY tensor path (232 TFLOP/s, profiles/r01g); here both
-// GEMMs of attention run on tcgen05 with TMEM accumulators:
+// Same arithmetic as attn_prefill.cu (transformers modeling_llama.py:199-222, fp32 softmax :217); both GEMMs of
+// attention run on tcgen05 with TMEM accumulators:
 //
-//   S  = Q K^T   M=128 query rows, N=128 keys, K=128 dims     A=Q (smem, K-major)  B=K  (smem, K-major)
-//   O += P V     M=128 query rows, N=128 dims, K=128 keys     A=P (smem, K-major)  B=V  (smem, MN-major)
+//   S  = Q K^T   M=128 query rows, N=64 keys,  K=128 dims     A=Q (smem, K-major)  B=K  (smem, K-major)
+//   O += P V     M=128 query rows, N=128 dims, K=64 keys      A=P (smem, K-major)  B=V  (smem, MN-major)
 //
-// One CTA = 128 query rows of one head. Warp 0: TMA producer (Q once; K and V page by page — a page of one
-// KV head is 16 rows x 256 B, loaded as two 128B-swizzled boxes — into 2-deep rings). Warp 1: the single
-// MMA-issuing thread. Warps 2-9: two threads per query row (each owns 64 of the tile's 128 keys; the two
-// halves of a row meet through a small smem exchange): read S from TMEM, causal mask, online softmax in
-// registers, write P as bf16 into the swizzled A-operand layout, rescale O in TMEM only when some row's
-// running max grew by more than 2^8 (lazy reference), finally normalise and store.
-// K runs one tile ahead of V in the producer (K0 K1 V0 K2 V1 ...), each with its own ring and barriers.
-// S is double-buffered in TMEM so QK^T of tile j+1 overlaps the softmax of tile j.
+// One CTA = TWO 128-row query tiles (A: rows m0.., B: rows m0+128..) of one head, worked in ping-pong: while the
+// four softmax warps of one tile are busy (TMEM -> registers, mask, max, ex2, P -> smem) the tensor core runs
+// the other tile's QK^T / PV, so neither side idles on the other. (The first version had one tile per CTA with
+// two threads per row; ncu showed the tensor pipe 31 % active and the softmax warps, with two block barriers
+// and a shared-memory exchange per tile, as the critical path: profiles/r01n.) Roles:
+//   warp 0      TMA producer: Q_A, Q_B once; K and V in 64-key tiles (four pages; a page of one KV head is
+//               16 rows x 256 B, two 128B-swizzled boxes), 3-deep rings, K one tile ahead of V
+//   warp 1      the single MMA-issuing thread: QK_A(j+1), QK_B(j+1), then PV_A(j), PV_B(j) as their P arrives
+//   warps 2-5   softmax of tile A, warps 6-9 of tile B: ONE thread per query row (no cross-thread exchange):
+//               64 scores from TMEM in one round trip, causal mask on diagonal tiles, running max with a lazy
+//               reference (O in TMEM is rescaled only when some row of the warp grew by more than 2^8), ex2,
+//               P as bf16 into the swizzled A-operand layout, finally O / l -> bf16
+// TMEM (512 columns): S_A x2, S_B x2 (64 columns each, double-buffered so QK^T(j+1) overlaps softmax(j)),
+// O_A, O_B (128 each). K and V tiles are shared by both query tiles: half the K/V shared-memory traffic per row.
 #include "common.cuh"
 
 #include <mutex>
@@ -24,16 +29,18 @@
 
 namespace atx {
 
-constexpr int kTcBM = 128;   // query rows per CTA
-constexpr int kTcBN = 128;   // keys per tile
+constexpr int kTcBM = 128;        // query rows per tile (two tiles per CTA)
+constexpr int kTcBN = 64;         // keys per tile
 constexpr int kTcD = 128;
-constexpr int kTcThreads = 320;   // TMA warp, MMA warp, 8 softmax warps
+constexpr int kTcThreads = 320;   // TMA warp, MMA warp, 4 + 4 softmax warps
 constexpr int kTcPage = 16;
-constexpr int kAtomBytes = 128 * 128;            // [128 rows x 64 bf16], 128B-swizzled
-constexpr int kTileBytes = 2 * kAtomBytes;       // [128 x 128] bf16 as two K- (or N-) atoms
-constexpr int kKS = 2;            // K ring depth (3 measured no faster: the kernel is bound by the softmax warps, not by loads)
-constexpr int kVS = 2;            // V ring depth
-constexpr int kTcSmem = (2 + kKS + kVS) * kTileBytes + 1024 + 256 + 1024;  // Q, K ring, V ring, P + align + barriers + exchange
+constexpr int kQAtom = 128 * 128;               // [128 rows x 64 bf16], 128B-swizzled: one K-atom of Q (or of P)
+constexpr int kQTile = 2 * kQAtom;              // [128 x 128] bf16
+constexpr int kKVAtom = kTcBN * 128;            // [64 rows x 64 bf16]
+constexpr int kKVTile = 2 * kKVAtom;            // [64 keys x 128 dims] bf16 as two dim-atoms
+constexpr int kPTile = kQAtom;                  // [128 rows x 64 keys] bf16
+constexpr int kKS = 3, kVS = 3;                 // ring depths
+constexpr int kTcSmem = 2 * kQTile + (kKS + kVS) * kKVTile + 2 * kPTile + 1024 + 512;   // + align + barriers
 
 // MN-major operand ([K rows][64 contiguous N elements] atoms, 128B swizzle): LBO = distance between the
 // N-atoms, SBO = distance between groups of 8 K-rows (cute::UMMA canonical Major-MN SW128 layout).
@@ -46,8 +53,6 @@ __device__ __forceinline__ uint64_t umma_desc_sw128_mn(uint32_t smem_addr, uint3
     d |= static_cast<uint64_t>(2) << 61;
     return d;
 }
-__device__ __forceinline__ void mbar_arrive_cnt(uint64_t* bar) { mbar_arrive(bar); }
-__device__ __forceinline__ void softmax_bar_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 __device__ __forceinline__ float ex2_approx(float x) {  // one MUFU op; 2^-inf = 0
     float y;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -62,32 +67,35 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                                ~static_cast<uintptr_t>(1023));
-    uint8_t* sQ = smem;
-    uint8_t* sK = smem + kTileBytes;                      // kKS stages
-    uint8_t* sV = smem + (1 + kKS) * kTileBytes;          // kVS stages
-    uint8_t* sP = smem + (1 + kKS + kVS) * kTileBytes;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (2 + kKS + kVS) * kTileBytes);
+    uint8_t* sQ = smem;                                   // tile A, tile B
+    uint8_t* sK = sQ + 2 * kQTile;                        // kKS stages
+    uint8_t* sV = sK + kKS * kKVTile;                     // kVS stages
+    uint8_t* sP = sV + kVS * kKVTile;                     // tile A, tile B
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * kPTile);
     uint64_t* q_full = bars;            // 1
-    uint64_t* k_full = bars + 1;        // 4 slots reserved
-    uint64_t* k_empty = bars + 5;       // 4
-    uint64_t* v_full = bars + 9;        // 4
-    uint64_t* v_empty = bars + 13;      // 4
-    uint64_t* s_full = bars + 17;       // 2
-    uint64_t* p_full = bars + 19;       // 1
-    uint64_t* o_done = bars + 20;       // 1
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 21);
+    uint64_t* k_full = bars + 1;        // 4 slots reserved each
+    uint64_t* k_empty = bars + 5;
+    uint64_t* v_full = bars + 9;
+    uint64_t* v_empty = bars + 13;
+    uint64_t* s_full = bars + 17;       // [tile][buffer]: 4
+    uint64_t* p_full = bars + 21;       // [tile]: 2
+    uint64_t* o_done = bars + 23;       // [tile]: 2
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 25);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int s = blockIdx.z, h = blockIdx.y;
     const int q_begin = cu_q[s];
     const int n_q = cu_q[s + 1] - q_begin;
-    const int m0 = blockIdx.x * kTcBM;
+    const int m0 = blockIdx.x * 2 * kTcBM;
     if (m0 >= n_q) return;  // whole CTA: before any barrier / TMEM use
     const int ctx = ctx_lens[s];
     const int off = ctx - n_q;  // query j sees keys [0, off + j]
     const int g = h / (Hq / Hkv);
-    const int kv_limit = min(ctx, off + m0 + kTcBM);
-    const int n_tiles = (kv_limit + kTcBN - 1) / kTcBN;
+    const bool has_b = m0 + kTcBM < n_q;                      // the second tile has at least one real row
+    // keys each tile needs, in 64-key tiles (B's rows see up to 128 more keys than A's)
+    const int nt_a = (min(ctx, off + m0 + kTcBM) + kTcBN - 1) / kTcBN;
+    const int nt_b = has_b ? (min(ctx, off + m0 + 2 * kTcBM) + kTcBN - 1) / kTcBN : 0;
+    const int n_tiles = max(nt_a, nt_b);
     const int* bt = block_table + static_cast<long long>(s) * max_blocks;
 
     if (warp == 0 && elect_one()) {
@@ -100,11 +108,12 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
             mbar_init(&k_empty[i], 1);
             mbar_init(&v_full[i], 1);
             mbar_init(&v_empty[i], 1);
+            mbar_init(&s_full[i], 1);
         }
-        mbar_init(&s_full[0], 1);
-        mbar_init(&s_full[1], 1);
-        mbar_init(p_full, 256);
-        mbar_init(o_done, 1);
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&p_full[i], 128);
+            mbar_init(&o_done[i], 1);
+        }
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc<512>(tmem_slot);
@@ -112,80 +121,74 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
-    const uint32_t tmem_S0 = tmem_base, tmem_O = tmem_base + 256;
+    // columns: S_A[0] 0, S_A[1] 64, S_B[0] 128, S_B[1] 192, O_A 256, O_B 384
     pdl_launch_dependents();
 
     if (warp == 0) {
-        // ===== TMA producer: the whole warp works. Lane p owns page p of the tile: the eight block-table
-        // lookups of a tile are one coalesced load (they were a chain of dependent single-thread loads in the
-        // first version, ~5000 cycles per tile), and lane p issues the four boxes (K/V x two 64-dim atoms).
+        // ===== TMA producer: the whole warp works. Lane p < 4 owns page p of a tile: the block-table lookups of
+        // a tile are one coalesced load, two tiles ahead of their use, and lane p issues its page's boxes.
         pdl_wait();  // q and this chunk's K/V rows come from the upstream kernels
         if (lane == 0) {
-            mbar_expect_tx(q_full, kTileBytes);
-            tma_load_2d(sQ, &tmQ, q_full, h * kTcD, q_begin + m0, kEvictNormal);
-            tma_load_2d(sQ + kAtomBytes, &tmQ, q_full, h * kTcD + 64, q_begin + m0, kEvictNormal);
+            mbar_expect_tx(q_full, has_b ? 2 * kQTile : kQTile);
+            for (int t = 0; t < (has_b ? 2 : 1); ++t) {
+                tma_load_2d(sQ + t * kQTile, &tmQ, q_full, h * kTcD, q_begin + m0 + t * kTcBM, kEvictNormal);
+                tma_load_2d(sQ + t * kQTile + kQAtom, &tmQ, q_full, h * kTcD + 64, q_begin + m0 + t * kTcBM,
+                            kEvictNormal);
+            }
         }
-        auto page_row = [&](int j) -> int {   // first cache row of this lane's page in tile j (or -1)
-            const int kv0 = j * kTcBN;
-            const int pages = min(kTcBN / kTcPage, (ctx - kv0 + kTcPage - 1) / kTcPage);
-            return (j < n_tiles && lane < pages) ? (__ldg(bt + kv0 / kTcPage + lane) * Hkv + g) * kTcPage : -1;
-        };
         auto tile_pages = [&](int j) { return min(kTcBN / kTcPage, (ctx - j * kTcBN + kTcPage - 1) / kTcPage); };
-        auto load_k = [&](int j, int row) {
-            const int ks = j % kKS;
-            if (lane == 0) {
-                mbar_wait(&k_empty[ks], ((j / kKS) & 1) ^ 1);
-                mbar_expect_tx(&k_full[ks], tile_pages(j) * kTcPage * 256);   // allocated pages only
-            }
-            __syncwarp();
-            if (row >= 0) {
-                uint8_t* dst = sK + ks * kTileBytes + lane * kTcPage * 128;
-                tma_load_2d(dst, &tmK, &k_full[ks], 0, row, kEvictLast);
-                tma_load_2d(dst + kAtomBytes, &tmK, &k_full[ks], 64, row, kEvictLast);
-            }
+        auto page_row = [&](int j) -> int {   // first cache row of this lane's page in tile j (or -1)
+            return (j < n_tiles && lane < tile_pages(j))
+                       ? (__ldg(bt + j * (kTcBN / kTcPage) + lane) * Hkv + g) * kTcPage : -1;
         };
-        auto load_v = [&](int j, int row) {
-            const int vs = j % kVS;
+        auto load = [&](int j, int row, uint8_t* ring, int depth, uint64_t* full, uint64_t* empty,
+                        const CUtensorMap* tm) {
+            const int st = j % depth;
             if (lane == 0) {
-                mbar_wait(&v_empty[vs], ((j / kVS) & 1) ^ 1);
-                mbar_expect_tx(&v_full[vs], tile_pages(j) * kTcPage * 256);
+                mbar_wait(&empty[st], ((j / depth) & 1) ^ 1);
+                mbar_expect_tx(&full[st], tile_pages(j) * kTcPage * 256);   // allocated pages only
             }
             __syncwarp();
             if (row >= 0) {
-                uint8_t* dst = sV + vs * kTileBytes + lane * kTcPage * 128;
-                tma_load_2d(dst, &tmV, &v_full[vs], 0, row, kEvictLast);
-                tma_load_2d(dst + kAtomBytes, &tmV, &v_full[vs], 64, row, kEvictLast);
+                uint8_t* dst = ring + st * kKVTile + lane * kTcPage * 128;
+                tma_load_2d(dst, tm, &full[st], 0, row, kEvictLast);
+                tma_load_2d(dst + kKVAtom, tm, &full[st], 64, row, kEvictLast);
             }
         };
         // K runs one tile ahead of V (QK^T of tile j+1 is issued before P.V of tile j): K0, K1, V0, K2, V1, ...
         int row_cur = page_row(0);
         int row_nxt = page_row(1);
-        load_k(0, row_cur);
+        load(0, row_cur, sK, kKS, k_full, k_empty, &tmK);
         for (int j = 0; j < n_tiles; ++j) {
-            const int row_nn = page_row(j + 2);   // block-table lookups stay two tiles ahead of their use
-            if (j + 1 < n_tiles) load_k(j + 1, row_nxt);
-            load_v(j, row_cur);
+            const int row_nn = page_row(j + 2);
+            if (j + 1 < n_tiles) load(j + 1, row_nxt, sK, kKS, k_full, k_empty, &tmK);
+            load(j, row_cur, sV, kVS, v_full, v_empty, &tmV);
             row_cur = row_nxt;
             row_nxt = row_nn;
         }
     } else if (warp == 1) {
         if (elect_one()) {
-            // ===== MMA issuer
+            // ===== MMA issuer. tcgen05.mma execute in issue order, which is what makes the S buffers safe:
+            // QK_X(j+1) overwrites S_X[(j+1)&1], last read by softmax_X(j-1), whose P the issuer has waited for.
             constexpr uint32_t idesc_qk = umma_idesc_bf16(kTcBM, kTcBN);                 // A, B K-major
             constexpr uint32_t idesc_pv = umma_idesc_bf16(kTcBM, kTcD) | (1u << 16);      // B (= V) MN-major
             auto issue_qk = [&](int j) {
                 const int st = j % kKS;
                 mbar_wait(&k_full[st], (j / kKS) & 1);
                 tc_fence_after();
-                const uint32_t qa = smem_u32(sQ), ka = smem_u32(sK + st * kTileBytes);
+                const uint32_t ka = smem_u32(sK + st * kKVTile);
 #pragma unroll
-                for (int kk = 0; kk < kTcD / 16; ++kk) {
-                    const uint32_t o = (kk >> 2) * kAtomBytes + (kk & 3) * 32;
-                    umma_bf16(tmem_S0 + (j & 1) * kTcBN, umma_desc_sw128(qa + o), umma_desc_sw128(ka + o), idesc_qk,
-                              kk > 0 ? 1u : 0u);
+                for (int t = 0; t < 2; ++t) {
+                    if (t == 0 ? j >= nt_a : j >= nt_b) continue;
+                    const uint32_t qa = smem_u32(sQ + t * kQTile);
+                    const uint32_t d_tmem = tmem_base + t * 128 + (j & 1) * kTcBN;
+#pragma unroll
+                    for (int kk = 0; kk < kTcD / 16; ++kk)
+                        umma_bf16(d_tmem, umma_desc_sw128(qa + (kk >> 2) * kQAtom + (kk & 3) * 32),
+                                  umma_desc_sw128(ka + (kk >> 2) * kKVAtom + (kk & 3) * 32), idesc_qk, kk > 0 ? 1u : 0u);
+                    umma_commit(&s_full[t * 2 + (j & 1)]);
                 }
                 umma_commit(&k_empty[st]);
-                umma_commit(&s_full[j & 1]);
             };
             mbar_wait(q_full, 0);
             issue_qk(0);
@@ -193,44 +196,47 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
                 if (j + 1 < n_tiles) issue_qk(j + 1);  // overlaps the softmax of tile j
                 const int st = j % kVS;
                 mbar_wait(&v_full[st], (j / kVS) & 1);
-                mbar_wait(p_full, j & 1);              // P(j) in smem, O rescaled, tail rows of V cleared
-                tc_fence_after();
-                const uint32_t pa = smem_u32(sP), va = smem_u32(sV + st * kTileBytes);
+                const uint32_t va = smem_u32(sV + st * kKVTile);
 #pragma unroll
-                for (int kk = 0; kk < kTcBN / 16; ++kk) {
-                    const uint64_t a_desc = umma_desc_sw128(pa + (kk >> 2) * kAtomBytes + (kk & 3) * 32);
-                    const uint64_t b_desc = umma_desc_sw128_mn(va + kk * 16 * 128, kAtomBytes);
-                    umma_bf16(tmem_O, a_desc, b_desc, idesc_pv, (j > 0 || kk > 0) ? 1u : 0u);
+                for (int t = 0; t < 2; ++t) {
+                    if (t == 0 ? j >= nt_a : j >= nt_b) continue;
+                    mbar_wait(&p_full[t], j & 1);          // P_t(j) in smem, O_t rescaled, tail rows of V cleared
+                    tc_fence_after();
+                    const uint32_t pa = smem_u32(sP + t * kPTile);
+#pragma unroll
+                    for (int kk = 0; kk < kTcBN / 16; ++kk)
+                        umma_bf16(tmem_base + 256 + t * 128, umma_desc_sw128(pa + kk * 32),
+                                  umma_desc_sw128_mn(va + kk * 16 * 128, kKVAtom), idesc_pv,
+                                  (j > 0 || kk > 0) ? 1u : 0u);
+                    umma_commit(&o_done[t]);
                 }
                 umma_commit(&v_empty[st]);
-                umma_commit(o_done);
             }
         }
     } else {
-        // ===== softmax / correction / epilogue: EIGHT warps, two per TMEM lane quarter. Thread (row, half)
-        // owns keys [64*half, 64*half+64) of its query row: 64 exponentials instead of 128 per thread and two
-        // warps per scheduler to hide MUFU / FMA latency (with four warps the kernel was softmax-bound at
-        // ~3000 cycles per tile against 1024 cycles of MMA). The two halves of a row exchange their partial
-        // maxima through shared memory; the partial sums are only combined at the very end.
+        // ===== softmax / correction / epilogue: warps 2-5 own tile A, warps 6-9 tile B; a warp reads the TMEM
+        // lane quarter (warp & 3), thread = one query row, all 64 keys of the tile in its registers.
+        const int t = (warp - 2) >> 2;                   // 0 = tile A, 1 = tile B
+        const int nt = t == 0 ? nt_a : nt_b;
         const int quarter = warp & 3;
-        const int half = (warp - 2) >> 2;               // 0 | 1
-        const int row = quarter * 32 + lane;            // row inside the tile == TMEM lane
-        const int qpos = m0 + row;                      // query index inside this sequence's chunk
-        const int limit = off + qpos;                   // last visible key
+        const int row = quarter * 32 + lane;             // row inside the tile == TMEM lane
+        const int qpos = m0 + t * kTcBM + row;           // query index inside this sequence's chunk
+        const int limit = off + qpos;                    // last visible key
+        const int first_limit = off + m0 + t * kTcBM;    // ... of the tile's first row (CTA-uniform per tile)
         const uint32_t lane_sel = static_cast<uint32_t>(quarter * 32) << 16;
-        float* xch = reinterpret_cast<float*>(tmem_slot + 4);  // [2][128] floats after the barriers
+        const uint32_t tmem_S = tmem_base + t * 128 + lane_sel;
+        const uint32_t tmem_O = tmem_base + 256 + t * 128 + lane_sel;
+        uint8_t* prow = sP + t * kPTile + row * 128;
         float m_run = -INFINITY, l_run = 0.f;
-        for (int j = 0; j < n_tiles; ++j) {
-            const int kv0 = j * kTcBN + half * 64;      // first key of this thread's half
-            mbar_wait(&s_full[j & 1], (j >> 1) & 1);
+        for (int j = 0; j < nt; ++j) {
+            const int kv0 = j * kTcBN;
+            mbar_wait(&s_full[t * 2 + (j & 1)], (j >> 1) & 1);
             tc_fence_after();
-            const uint32_t ts = tmem_S0 + (j & 1) * kTcBN + half * 64 + lane_sel;
             uint32_t sv[4][16];                          // 64 scores: one TMEM round trip
 #pragma unroll
-            for (int c = 0; c < 4; ++c) tmem_ld16(ts + c * 16, sv[c]);
+            for (int c = 0; c < 4; ++c) tmem_ld16(tmem_S + (j & 1) * kTcBN + c * 16, sv[c]);
             tmem_ld_wait();
-            const bool diag = j * kTcBN + kTcBN - 1 > off + m0;  // tile touches the causal boundary (CTA-uniform)
-            if (diag) {
+            if (kv0 + kTcBN - 1 > first_limit) {         // tile touches the causal boundary
 #pragma unroll
                 for (int c = 0; c < 4; ++c)
 #pragma unroll
@@ -242,15 +248,11 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
             for (int c = 0; c < 4; ++c)
 #pragma unroll
                 for (int i = 0; i < 16; ++i) mx4[i & 3] = fmaxf(mx4[i & 3], __uint_as_float(sv[c][i]));
-            const float mx_mine = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
-            xch[half * 128 + row] = mx_mine;
-            softmax_bar_sync();
-            const float mx = fmaxf(mx_mine, xch[(half ^ 1) * 128 + row]);
+            const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
             // Lazy reference update: the exponent reference only moves when some row of this warp saw its
             // maximum grow by more than 2^8 relative to it (P stays <= 256, exact in fp32 and fine in bf16; l
-            // accumulates against the same reference, so the final O / l is unchanged). Rescaling O in TMEM
-            // costs ~1000 cycles on the critical path and was taken on 97 % of tiles with an eager update.
-            // Both warps of a row quarter see the same maxima, so they take the same branch.
+            // accumulates against the same reference, so the final O / l is unchanged). Rescaling O in TMEM is a
+            // full round trip on the critical path and was taken on 97 % of tiles with an eager update.
             const float cand = mx * scale_log2;  // -inf when the row has seen nothing in this tile
             float corr = 1.f;
             const bool moved = __any_sync(0xffffffffu, cand > m_run + 8.f);
@@ -271,10 +273,9 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
                     sv[c][i >> 1] = pack_bf16(p0, p1);
                 }
             l_run = l_run * corr + (ls4[0] + ls4[1]) + (ls4[2] + ls4[3]);
-            // the previous P.V must have retired before P is overwritten or O is touched
-            if (j > 0) mbar_wait(o_done, (j - 1) & 1);
+            // the previous P.V of this tile must have retired before P is overwritten or O is touched
+            if (j > 0) mbar_wait(&o_done[t], (j - 1) & 1);
             tc_fence_after();
-            uint8_t* prow = sP + half * kAtomBytes + row * 128;   // this half == one 64-key atom of P
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
                 const int ch = c * 2;  // the two 16-byte chunks of these 16 keys
@@ -283,60 +284,61 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
                 *reinterpret_cast<uint4*>(prow + (((ch + 1) ^ (row & 7)) << 4)) =
                     make_uint4(sv[c][4], sv[c][5], sv[c][6], sv[c][7]);
             }
-            // rescale this half's 64 columns of O only if some row of the warp moved its maximum
+            // rescale this row of O only if some row of the warp moved its maximum
             if (j > 0 && moved) {
 #pragma unroll 1
-                for (int c = 0; c < 64; c += 16) {
+                for (int c = 0; c < kTcD; c += 16) {
                     uint32_t v[16];
-                    tmem_ld16(tmem_O + lane_sel + half * 64 + c, v);
+                    tmem_ld16(tmem_O + c, v);
                     tmem_ld_wait();
 #pragma unroll
                     for (int i = 0; i < 16; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) * corr);
-                    tmem_st16(tmem_O + lane_sel + half * 64 + c, v);
+                    tmem_st16(tmem_O + c, v);
                 }
                 tmem_st_wait();
             }
             // keys past the context in the last tile: their V rows are stale page contents or never-loaded
-            // shared memory; P is 0 there but 0 * NaN would poison O, so clear those rows (dim-atom `half`)
-            if (j * kTcBN + kTcBN > ctx) {
+            // shared memory; P is 0 there but 0 * NaN would poison O, so clear those rows (both dim-atoms)
+            if (kv0 + kTcBN > ctx) {
                 mbar_wait(&v_full[j % kVS], (j / kVS) & 1);
-                const int valid = ctx - j * kTcBN;
-                if (row >= valid) {
-                    uint8_t* vrow = sV + (j % kVS) * kTileBytes + half * kAtomBytes + row * 128;
+                const int valid = ctx - kv0;
+                if (row < kTcBN && row >= valid) {
+                    uint8_t* vrow = sV + (j % kVS) * kKVTile + row * 128;
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) *reinterpret_cast<uint4*>(vrow + i * 16) = make_uint4(0, 0, 0, 0);
+                    for (int i = 0; i < 8; ++i) {
+                        *reinterpret_cast<uint4*>(vrow + i * 16) = make_uint4(0, 0, 0, 0);
+                        *reinterpret_cast<uint4*>(vrow + kKVAtom + i * 16) = make_uint4(0, 0, 0, 0);
+                    }
                 }
             }
             fence_proxy_async();   // generic-proxy smem writes (P, cleared V rows) -> visible to the tensor core
             tc_fence_before();
-            mbar_arrive_cnt(p_full);
-            softmax_bar_sync();    // both halves have read this tile's exchanged maxima before the next write
+            mbar_arrive(&p_full[t]);
         }
-        // ---- epilogue: O / l -> bf16 (each half stores 64 dims of its row)
-        xch[half * 128 + row] = l_run;
-        softmax_bar_sync();
-        const float l_tot = l_run + xch[(half ^ 1) * 128 + row];
-        mbar_wait(o_done, (n_tiles - 1) & 1);
-        tc_fence_after();
-        const float inv = l_tot > 0.f ? 1.f / l_tot : 0.f;
-        __nv_bfloat16* orow = out + (static_cast<long long>(q_begin + qpos) * Hq + h) * kTcD + half * 64;
+        // ---- epilogue: O / l -> bf16, one 256-byte row per thread
+        if (nt > 0) {
+            mbar_wait(&o_done[t], (nt - 1) & 1);
+            tc_fence_after();
+            const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
+            __nv_bfloat16* orow = out + (static_cast<long long>(q_begin + qpos) * Hq + h) * kTcD;
 #pragma unroll 1
-        for (int c = 0; c < 64; c += 16) {
-            uint32_t v[16];
-            tmem_ld16(tmem_O + lane_sel + half * 64 + c, v);
-            tmem_ld_wait();
-            if (qpos < n_q) {
-                uint4 a, b;
-                a.x = pack_bf16(__uint_as_float(v[0]) * inv, __uint_as_float(v[1]) * inv);
-                a.y = pack_bf16(__uint_as_float(v[2]) * inv, __uint_as_float(v[3]) * inv);
-                a.z = pack_bf16(__uint_as_float(v[4]) * inv, __uint_as_float(v[5]) * inv);
-                a.w = pack_bf16(__uint_as_float(v[6]) * inv, __uint_as_float(v[7]) * inv);
-                b.x = pack_bf16(__uint_as_float(v[8]) * inv, __uint_as_float(v[9]) * inv);
-                b.y = pack_bf16(__uint_as_float(v[10]) * inv, __uint_as_float(v[11]) * inv);
-                b.z = pack_bf16(__uint_as_float(v[12]) * inv, __uint_as_float(v[13]) * inv);
-                b.w = pack_bf16(__uint_as_float(v[14]) * inv, __uint_as_float(v[15]) * inv);
-                *reinterpret_cast<uint4*>(orow + c) = a;
-                *reinterpret_cast<uint4*>(orow + c + 8) = b;
+            for (int c = 0; c < kTcD; c += 16) {
+                uint32_t v[16];
+                tmem_ld16(tmem_O + c, v);
+                tmem_ld_wait();
+                if (qpos < n_q) {
+                    uint4 a, b;
+                    a.x = pack_bf16(__uint_as_float(v[0]) * inv, __uint_as_float(v[1]) * inv);
+                    a.y = pack_bf16(__uint_as_float(v[2]) * inv, __uint_as_float(v[3]) * inv);
+                    a.z = pack_bf16(__uint_as_float(v[4]) * inv, __uint_as_float(v[5]) * inv);
+                    a.w = pack_bf16(__uint_as_float(v[6]) * inv, __uint_as_float(v[7]) * inv);
+                    b.x = pack_bf16(__uint_as_float(v[8]) * inv, __uint_as_float(v[9]) * inv);
+                    b.y = pack_bf16(__uint_as_float(v[10]) * inv, __uint_as_float(v[11]) * inv);
+                    b.z = pack_bf16(__uint_as_float(v[12]) * inv, __uint_as_float(v[13]) * inv);
+                    b.w = pack_bf16(__uint_as_float(v[14]) * inv, __uint_as_float(v[15]) * inv);
+                    *reinterpret_cast<uint4*>(orow + c) = a;
+                    *reinterpret_cast<uint4*>(orow + c + 8) = b;
+                }
             }
         }
     }
@@ -416,7 +418,7 @@ int launch_prefill_tc(const void* q, const void* kc, const void* vc, const int* 
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = (flags & ATX_FLAG_PDL) ? 1 : 0;
-    cfg.gridDim = dim3(static_cast<unsigned>((max_q_len + kTcBM - 1) / kTcBM), static_cast<unsigned>(Hq),
+    cfg.gridDim = dim3(static_cast<unsigned>((max_q_len + 2 * kTcBM - 1) / (2 * kTcBM)), static_cast<unsigned>(Hq),
                        static_cast<unsigned>(S));
     cfg.blockDim = dim3(kTcThreads);
     cfg.dynamicSmemBytes = kTcSmem;

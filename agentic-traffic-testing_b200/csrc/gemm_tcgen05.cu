@@ -59,25 +59,11 @@ __device__ __forceinline__ float dsmem_ld(uint32_t remote_addr) {
     return v;
 }
 
-// Internal epilogue mode of atx_gemm_qkv_rope_kv: the tile is one attention head (head_dim 128 = kBM); q and k
-// heads are rotated (RoPE, modeling_llama.py:138-168) and q goes out as bf16 while k / v go straight into
-// their KV-cache pages (slot mapping), so the fp32 qkv round trip and the separate RoPE kernel disappear.
-constexpr int kModeQkvRope = 4;
-struct RopeArgs {
-    const int* positions;
-    const int* slots;
-    const float* cos_sin;
-    __nv_bfloat16* q_out;
-    __nv_bfloat16* k_cache;
-    __nv_bfloat16* v_cache;
-    int Hq, Hkv, block_size;
-};
-
 template <int TN>
 __global__ void __launch_bounds__(kGemmThreads)
 gemm_wt_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmX,
                void* __restrict__ out, long long ldo, int T, int N, int kb_total, int kb_per_split,
-               int mode, int w_evict_first, int l2_prefetch_kb, int stages, const RopeArgs ra) {
+               int mode, int w_evict_first, int l2_prefetch_kb, int stages) {
     // `stages` (<= Cfg::kStages) is the ring depth actually used: CTAs with few k-blocks get a smaller
     // shared-memory footprint, so more of them are resident per SM
     using Cfg = GemmCfg<TN>;
@@ -190,7 +176,7 @@ gemm_wt_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
         mbar_wait(accum_bar, 0);
         tc_fence_after();
         pdl_wait();  // `out` may be the residual stream written by the upstream grid
-        const bool nonlinear = mode == ATX_GEMM_SWIGLU_BF16 || mode == kModeQkvRope;
+        const bool nonlinear = mode == ATX_GEMM_SWIGLU_BF16;
         if (nonlinear && gridDim.z > 1) {
             // Split-K with a nonlinear epilogue: the gridDim.z CTAs of this tile form ONE thread-block
             // cluster (launch attribute). CTAs 1.. park their partial accumulator in their own (idle) stage
@@ -234,69 +220,6 @@ gemm_wt_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
         }
         if (nonlinear && blockIdx.z != 0) {
             // cluster peer: its sum now lives in the leader's accumulator
-        } else if (mode == kModeQkvRope) {
-            // lane = head dimension d; the rotation partner d ^ 64 lives in warp ^ 2: cross through shared memory
-            float* sx = reinterpret_cast<float*>(smem);   // [TN][128]
-            const int d = warp * 32 + lane;
-            const int head = blockIdx.x;
-            const uint32_t tl = tmem_acc + (static_cast<uint32_t>(warp * 32) << 16);
-#pragma unroll 1
-            for (int c = 0; c < TN; c += 16) {
-                if (t0 + c >= T) break;
-                uint32_t v[16];
-                tmem_ld16(tl + c, v);
-                tmem_ld_wait();
-#pragma unroll
-                for (int j = 0; j < 16; ++j) sx[(c + j) * kBM + d] = __uint_as_float(v[j]);
-            }
-            __syncthreads();
-            const bool is_q = head < ra.Hq, is_v = head >= ra.Hq + ra.Hkv;
-            const int kvh = is_v ? head - ra.Hq - ra.Hkv : head - ra.Hq;
-            const int i = d & 63;
-            const int t_end = min(T, t0 + TN);
-            // tokens in groups of 8 with every dependent load of the group issued before the first use: a decode
-            // step has a handful of tokens and each costs two dependent global loads (position -> cos/sin)
-            constexpr int U = 8;
-#pragma unroll 1
-            for (int tb = t0; tb < t_end; tb += U) {
-                int pos[U], slot[U];
-#pragma unroll
-                for (int u = 0; u < U; ++u) {
-                    const bool valid = tb + u < t_end;
-                    pos[u] = (valid && !is_v) ? ra.positions[tb + u] : 0;
-                    slot[u] = valid ? (is_q ? 0 : ra.slots[tb + u]) : -1;
-                }
-                float cv[U], sv[U];
-#pragma unroll
-                for (int u = 0; u < U; ++u) {
-                    const float* cs = ra.cos_sin + static_cast<long long>(pos[u]) * kBM;
-                    cv[u] = is_v ? 1.f : cs[i];
-                    sv[u] = is_v ? 0.f : cs[64 + i];
-                }
-#pragma unroll
-                for (int u = 0; u < U; ++u) {
-                    const int t = tb + u;
-                    const bool valid = t < t_end;     // warp-uniform, like slot[u]
-                    const float mine = valid ? sx[(t - t0) * kBM + d] : 0.f;
-                    float o = mine;
-                    if (!is_v) {
-                        const float other = valid ? sx[(t - t0) * kBM + (d ^ 64)] : 0.f;
-                        // q*cos + rotate_half(q)*sin, products rounded separately as the reference does
-                        o = __fadd_rn(__fmul_rn(mine, cv[u]), __fmul_rn(d < 64 ? -other : other, sv[u]));
-                    }
-                    const float o_next = __shfl_down_sync(0xffffffffu, o, 1);
-                    if (!valid || slot[u] < 0) continue;   // beyond T, or a padded row: nothing to write
-                    __nv_bfloat16* dst;
-                    if (is_q) {
-                        dst = ra.q_out + (static_cast<long long>(t) * ra.Hq + head) * kBM;
-                    } else {
-                        const long long blk = slot[u] / ra.block_size;
-                        const int off = slot[u] % ra.block_size;
-                        dst = (is_v ? ra.v_cache : ra.k_cache) + ((blk * ra.Hkv + kvh) * ra.block_size + off) * kBM;
-                    }
-                    if ((lane & 1) == 0) *reinterpret_cast<uint32_t*>(dst + d) = pack_bf16(o, o_next);
-                }
-            }
         } else if (mode == ATX_GEMM_SWIGLU_BF16) {
             // Rows [0,64) of this tile are gate features, rows [64,128) the matching up features
             // (weights interleaved in 64-row groups at load time): act = silu(gate) * up, bf16.
@@ -673,7 +596,7 @@ static int g_l2_prefetch_kb = 0;  // measured on B200: prefetching ahead of the 
 
 template <int TN>
 static int launch_gemm(const atx_gemm_plan* p, int ti, void* out, long long ldo, int T, int mode,
-                       int splits, int pdl, cudaStream_t stream, const RopeArgs& ra = RopeArgs{}) {
+                       int splits, int pdl, cudaStream_t stream) {
     using Cfg = GemmCfg<TN>;
     static bool attr_done[64] = {false};  // per instantiation and device; benign race (idempotent call)
     int dev = 0;
@@ -689,8 +612,8 @@ static int launch_gemm(const atx_gemm_plan* p, int ti, void* out, long long ldo,
     int stages = kb_per < Cfg::kStages ? kb_per : Cfg::kStages;
     // the fused-SwiGLU epilogue parks half a tile in the stage buffers: keep them large enough
     // (a whole fp32 tile when the split-K cluster parks partial sums there)
-    if (mode == ATX_GEMM_SWIGLU_BF16 || mode == kModeQkvRope) {
-        const int need = (TN * ((zs > 1 || mode == kModeQkvRope) ? kBM : 64) * 4 + Cfg::kStageBytes - 1) / Cfg::kStageBytes;
+    if (mode == ATX_GEMM_SWIGLU_BF16) {
+        const int need = (TN * (zs > 1 ? kBM : 64) * 4 + Cfg::kStageBytes - 1) / Cfg::kStageBytes;
         if (stages < need) stages = need;
     }
     const int smem_bytes = stages * Cfg::kStageBytes + 1024 + 256;
@@ -707,7 +630,7 @@ static int launch_gemm(const atx_gemm_plan* p, int ti, void* out, long long ldo,
         attr[na].val.programmaticStreamSerializationAllowed = 1;
         ++na;
     }
-    if ((mode == ATX_GEMM_SWIGLU_BF16 || mode == kModeQkvRope) && zs > 1) {  // the K-splits of one tile are one cluster (DSMEM reduction)
+    if (mode == ATX_GEMM_SWIGLU_BF16 && zs > 1) {  // the K-splits of one tile are one cluster (DSMEM reduction)
         attr[na].id = cudaLaunchAttributeClusterDimension;
         attr[na].val.clusterDim.x = 1;
         attr[na].val.clusterDim.y = 1;
@@ -718,7 +641,7 @@ static int launch_gemm(const atx_gemm_plan* p, int ti, void* out, long long ldo,
     cfg.numAttrs = na;
     ATX_CUDA(cudaLaunchKernelEx(&cfg, gemm_wt_kernel<TN>, p->tmW, p->tmX[ti], out, ldo, T,
                                 static_cast<int>(p->N), kb_total, kb_per, mode, p->w_evict_first,
-                                pdl ? tl_l2_prefetch_kb : 0, stages, ra));
+                                pdl ? tl_l2_prefetch_kb : 0, stages));
     return ATX_OK;
 }
 
@@ -752,12 +675,6 @@ static int launch_gemm_persistent(const atx_gemm_plan* p, int ti, void* out, lon
                                 static_cast<int>(p->N), kb_total, tiles_t, total, mode, p->w_evict_first));
     return ATX_OK;
 }
-
-// ATX_GEMM_PERSISTENT=0 keeps the one-tile-per-CTA kernel for prefill-sized batches too
-static const bool g_gemm_persistent = [] {
-    const char* e = getenv("ATX_GEMM_PERSISTENT");
-    return !(e && e[0] == '0');
-}();
 
 extern "C" {
 
@@ -835,40 +752,10 @@ int atx_gemm_run(const atx_gemm_plan* p, void* out, long long ldo, int T, int mo
     if (T <= 16) return launch_gemm<16>(p, 0, out, ldo, T, mode, splits, pdl, stream);
     if (T <= 32) return launch_gemm<32>(p, 1, out, ldo, T, mode, splits, pdl, stream);
     if (T <= 64) return launch_gemm<64>(p, 2, out, ldo, T, mode, splits, pdl, stream);
-    if (g_gemm_persistent && splits == 1) {
-        if (T <= 128) return launch_gemm_persistent<128>(p, 3, out, ldo, T, mode, pdl, stream);
-        return launch_gemm_persistent<256>(p, 4, out, ldo, T, mode, pdl, stream);
-    }
-    if (T <= 128) return launch_gemm<128>(p, 3, out, ldo, T, mode, splits, pdl, stream);
-    return launch_gemm<256>(p, 4, out, ldo, T, mode, splits, pdl, stream);
-}
-
-int atx_gemm_qkv_rope_kv(const atx_gemm_plan* p, int T, const int* positions, const int* slots, const float* cos_sin,
-                         void* q_out, void* k_cache, void* v_cache, int Hq, int Hkv, int D, int block_size, int splits,
-                         int flags, atx_stream_t stream_) {
-    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
-    ATX_REQUIRE(p && positions && slots && cos_sin && q_out && k_cache && v_cache, "atx_gemm_qkv_rope_kv: null pointer");
-    ATX_REQUIRE(D == kBM, "atx_gemm_qkv_rope_kv: head_dim %d unsupported (one %d-row tile per head)", D, kBM);
-    ATX_REQUIRE(Hq > 0 && Hkv > 0 && block_size > 0 && p->N == static_cast<long long>(Hq + 2 * Hkv) * D,
-                "atx_gemm_qkv_rope_kv: plan has N=%lld, expected (Hq + 2 Hkv) * D = %lld", p->N,
-                static_cast<long long>(Hq + 2 * Hkv) * D);
-    ATX_REQUIRE(T > 0 && T <= p->T_cap && T <= 64, "atx_gemm_qkv_rope_kv: T=%d outside (0, min(64, %lld)]", T, p->T_cap);
-    const int kb_total = static_cast<int>(p->K / kBK);
-    if (splits <= 0) {
-        splits = 1;
-        const int want = atx_gemm_auto_splits(p->N, p->K, T);
-        while (splits * 2 <= want && splits * 2 <= 8 && kb_total % (splits * 2) == 0) splits *= 2;
-    }
-    ATX_REQUIRE(splits <= 8 && (splits & (splits - 1)) == 0 && kb_total % splits == 0,
-                "atx_gemm_qkv_rope_kv: splits=%d must be 1, 2, 4 or 8 and divide K/64=%d", splits, kb_total);
-    RopeArgs ra = {positions, slots, cos_sin, reinterpret_cast<__nv_bfloat16*>(q_out),
-                   reinterpret_cast<__nv_bfloat16*>(k_cache), reinterpret_cast<__nv_bfloat16*>(v_cache), Hq, Hkv,
-                   block_size};
-    const int pdl = (flags & ATX_FLAG_PDL) ? 1 : 0;
-    tl_l2_prefetch_kb = ((flags >> 8) & 0xff) ? ((flags >> 8) & 0xff) : g_l2_prefetch_kb;
-    if (T <= 16) return launch_gemm<16>(p, 0, q_out, 0, T, kModeQkvRope, splits, pdl, stream, ra);
-    if (T <= 32) return launch_gemm<32>(p, 1, q_out, 0, T, kModeQkvRope, splits, pdl, stream, ra);
-    return launch_gemm<64>(p, 2, q_out, 0, T, kModeQkvRope, splits, pdl, stream, ra);
+    // prefill-sized batches: the persistent, warp-specialised kernel (one CTA per SM, two TMEM accumulators)
+    ATX_REQUIRE(splits == 1, "atx_gemm_run: split-K is for decode-sized steps (T <= 64); got T=%d splits=%d", T, splits);
+    if (T <= 128) return launch_gemm_persistent<128>(p, 3, out, ldo, T, mode, pdl, stream);
+    return launch_gemm_persistent<256>(p, 4, out, ldo, T, mode, pdl, stream);
 }
 
 }  // extern "C"

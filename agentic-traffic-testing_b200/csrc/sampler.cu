@@ -64,6 +64,27 @@ __device__ __forceinline__ float block_sum(float v, float* sh) {
     return r;
 }
 
+// Visit every logit of a row: 16-byte loads, four in flight per thread, when the row allows it (the 128 256-wide
+// rows of the Llama vocabulary do). A pass over a row is a chain of L2 round trips, not bandwidth: with scalar
+// loads one after another the arg-max pass alone took 20 us.
+template <class F>
+__device__ __forceinline__ void for_each_logit(const float* __restrict__ row, int V, bool vec, F f) {
+    if (vec) {
+        const float4* r4 = reinterpret_cast<const float4*>(row);
+        const int n4 = V >> 2;
+#pragma unroll 4
+        for (int j = threadIdx.x; j < n4; j += kSampThreads) {
+            const float4 v = __ldg(r4 + j);
+            f(v.x, 4 * j);
+            f(v.y, 4 * j + 1);
+            f(v.z, 4 * j + 2);
+            f(v.w, 4 * j + 3);
+        }
+    } else {
+        for (int i = threadIdx.x; i < V; i += kSampThreads) f(row[i], i);
+    }
+}
+
 __global__ void __launch_bounds__(kSampThreads)
 sample_kernel(const float* __restrict__ logits, long long ldl, const float* __restrict__ temperature,
               const float* __restrict__ top_p, const unsigned long long* __restrict__ seeds,
@@ -75,10 +96,11 @@ sample_kernel(const float* __restrict__ logits, long long ldl, const float* __re
     const int b = blockIdx.x;
     const float* row = logits + static_cast<long long>(b) * ldl;
     const float T = temperature ? temperature[b] : 0.f;
+    const bool vec = (V & 3) == 0 && (reinterpret_cast<uintptr_t>(row) & 15) == 0;
 
     // pass 1: arg-max of the raw logits (also the softmax shift)
     ArgMax am = {-INFINITY, 0x7fffffff};
-    for (int i = threadIdx.x; i < V; i += kSampThreads) am = better(am, ArgMax{row[i], i});
+    for_each_logit(row, V, vec, [&](float l, int i) { am = better(am, ArgMax{l, i}); });
     am = block_argmax(am, sh_am);
     if (!(T > 0.f)) {
         if (threadIdx.x == 0) out_ids[b] = am.i;
@@ -91,7 +113,7 @@ sample_kernel(const float* __restrict__ logits, long long ldl, const float* __re
     float thr = 0.f;  // keep e_i >= thr, e_i = exp((l_i - lmax) / T) in (0, 1]
     if (P < 1.f) {
         float z = 0.f;
-        for (int i = threadIdx.x; i < V; i += kSampThreads) z += expf((row[i] - lmax) * inv_t);
+        for_each_logit(row, V, vec, [&](float l, int) { z += expf((l - lmax) * inv_t); });
         z = block_sum(z, sh_f);
         const float target = P * z;
         // smallest float x in [0, 1] with sum_{e_j > x} e_j < target
@@ -100,10 +122,10 @@ sample_kernel(const float* __restrict__ logits, long long ldl, const float* __re
             const uint32_t mid = lo + (hi - lo) / 2;
             const float x = __uint_as_float(mid);
             float s = 0.f;
-            for (int i = threadIdx.x; i < V; i += kSampThreads) {
-                const float e = expf((row[i] - lmax) * inv_t);
+            for_each_logit(row, V, vec, [&](float l, int) {
+                const float e = expf((l - lmax) * inv_t);
                 s += e > x ? e : 0.f;
-            }
+            });
             s = block_sum(s, sh_f);
             if (s < target) hi = mid; else lo = mid;
         }
@@ -115,11 +137,10 @@ sample_kernel(const float* __restrict__ logits, long long ldl, const float* __re
     const uint32_t key = lowbias32(static_cast<uint32_t>(seed) + 0x9E3779B9u * step) ^
                          lowbias32(static_cast<uint32_t>(seed >> 32) ^ 0x85EBCA6Bu);
     ArgMax best = {-INFINITY, 0x7fffffff};
-    for (int i = threadIdx.x; i < V; i += kSampThreads) {
-        const float l = row[i];
-        if (thr > 0.f && !(expf((l - lmax) * inv_t) >= thr)) continue;
+    for_each_logit(row, V, vec, [&](float l, int i) {
+        if (thr > 0.f && !(expf((l - lmax) * inv_t) >= thr)) return;
         best = better(best, ArgMax{l * inv_t + gumbel(key, static_cast<uint32_t>(i)), i});
-    }
+    });
     best = block_argmax(best, sh_am);
     if (threadIdx.x == 0) out_ids[b] = best.i < V ? best.i : am.i;
 }

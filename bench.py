@@ -33,7 +33,8 @@ os.environ.setdefault("LLM_IGNORE_EOS", "1")
 # NCCL's own log stays on (the driver counts the ranks of each communicator from it) without touching stdout, which
 # carries the one JSON line: every process logs to a file of its own and replays the communicator lines on stderr
 # when it exits. (Pointing NCCL at /dev/stderr re-opens and truncates whatever file stderr was redirected to.)
-os.environ.setdefault("NCCL_DEBUG", "INFO")
+if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":   # (the image's default: a banner on stdout)
+    os.environ["NCCL_DEBUG"] = "INFO"
 os.environ.setdefault("NCCL_DEBUG_SUBSYS", "INIT")
 if "NCCL_DEBUG_FILE" not in os.environ and os.environ["NCCL_DEBUG"].upper() not in ("WARN", "VERSION"):
     import atexit

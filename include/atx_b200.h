@@ -64,16 +64,6 @@ void atx_gemm_plan_destroy(atx_gemm_plan* plan);
 int atx_gemm_run(const atx_gemm_plan* plan, void* out, long long ldo, int T, int mode, int splits,
                  int flags, atx_stream_t stream);
 int atx_gemm_auto_splits(long long N, long long K, int T);
-/* Fused q/k/v projection + RoPE + KV-cache write for decode-sized steps (T <= 64, head_dim 128): the plan's W is
- * the fused [(Hq + 2 Hkv) * 128, K] q/k/v weight, so every 128-row GEMM tile is one head. The epilogue rotates
- * q and k heads (apply_rotary_pos_emb, modeling_llama.py:146-168, same arithmetic as atx_rope_kv_write: table
- * lookup, separately rounded products), writes q as bf16 [T, Hq * 128] and scatters k / v into their cache pages
- * by slot (slot < 0: row skipped) — replacing atx_gemm_run(STORE/ADD_F32) + atx_rope_kv_write and the fp32 qkv
- * buffer between them. splits: 0 = choose, else 1/2/4/8 dividing K/64; split-K runs as a thread-block cluster
- * reduced through distributed shared memory (no atomics, no zeroed workspace). */
-int atx_gemm_qkv_rope_kv(const atx_gemm_plan* plan, int T, const int* positions, const int* slots,
-                         const float* cos_sin, void* q_out, void* k_cache, void* v_cache, int Hq, int Hkv, int D,
-                         int block_size, int splits, int flags, atx_stream_t stream);
 /* Tuning knob: how many 16 KB weight slices a CTA launched with ATX_FLAG_PDL prefetches into L2
  * before it waits for the upstream kernel (default 0 = off: it measured slower on B200). Process-wide. */
 void atx_gemm_set_l2_prefetch(int k_blocks);
@@ -157,7 +147,8 @@ int atx_silu_mul(const float* gu, void* act, int T, int I, int flags, atx_stream
  * :217) over vLLM's paged KV (FlashInfer decode). q: [B, Hq * D] bf16; out: [B, Hq * D] bf16;
  * block_table: [B, max_blocks] int32; seq_lens[B] = tokens in cache INCLUDING the current one.
  * workspace: fp32 scratch of atx_paged_attn_decode_workspace_bytes(B, Hq, D, num_splits) bytes,
- * supplied by the caller (partial outputs + running max / sum per split). */
+ * supplied by the caller (partial outputs + running max / sum per split).
+ * head_dim 64 | 128, at most 8 query heads per KV head, block_size a multiple of 16 (else ATX_ERR_UNSUPPORTED). */
 long long atx_paged_attn_decode_workspace_bytes(int B, int Hq, int D, int num_splits);
 int atx_paged_attn_decode(const void* q, const void* k_cache, const void* v_cache, const int* block_table,
                           const int* seq_lens, void* out, void* workspace, long long workspace_bytes,

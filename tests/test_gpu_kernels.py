@@ -590,61 +590,14 @@ def test_allreduce_ll_one_gpu_fake_peers(cabi, T, H, world, use_rows):
             1e-5, None, 0, 0, st))
 
 
-@pytest.mark.parametrize("T,Hq,Hkv,K,splits", [(1, 4, 1, 512, 1), (6, 32, 8, 4096, 0), (16, 8, 1, 8192, 8),
-                                               (23, 4, 2, 1024, 4), (33, 8, 2, 512, 2), (64, 4, 1, 2048, 0)])
-def test_gemm_qkv_rope_kv_fused_epilogue(cabi, T, Hq, Hkv, K, splits):
-    """q/k/v projection with RoPE and the KV-page scatter in the GEMM epilogue (head_dim 128; split-K as a
-    cluster reduced through DSMEM) against the oracle's projection -> rope -> bf16 -> slot scatter on the same
-    bf16 operands. Integer work (which page, which row) is exact: untouched pages keep their NaN poison, padded
-    rows (slot -1) write nothing."""
-    D, bs, nblocks = 128, 16, 9
-    s = R.shape_by_name("8b")
-    g = torch.Generator().manual_seed(T * 7 + Hq + K)
-    N = (Hq + 2 * Hkv) * D
-    w = _bf16(torch.randn(N, K, generator=g) * 0.03)
-    x = _bf16(torch.randn(T, K, generator=g))
-    positions = torch.randint(0, 30000, (T,), generator=g, dtype=torch.int32)
-    perm = torch.randperm(nblocks * bs, generator=g)[:T].to(torch.int32)
-    slots = perm.clone()
-    if T > 2:
-        slots[T // 2] = -1                                     # a padded row
-    cs = R.cos_sin_table(s, 32768)
-    xb = torch.full((max(T, 8) + 2, K), float("nan"), dtype=torch.bfloat16, device="cuda")
-    xb[:T] = x.cuda()
-    plan = cabi.GemmPlan(w.cuda().contiguous(), xb)
-    kc = torch.full((nblocks, Hkv, bs, D), float("nan"), dtype=torch.bfloat16, device="cuda")
-    vc = torch.full_like(kc, float("nan"))
-    qo = torch.full((T, Hq * D), float("nan"), dtype=torch.bfloat16, device="cuda")
-    cabi.gemm_qkv_rope_kv(plan, T, positions.cuda(), slots.cuda(), cs.cuda(), qo, kc, vc, Hq, Hkv, D, bs, splits)
-    torch.cuda.synchronize()
-    qkv = x.float() @ w.float().T
-    cos, sin = R.rope_cos_sin(positions, R.llama3_inv_freq(s))
-    q_ref = R.apply_rope(qkv[:, : Hq * D].view(T, Hq, D), cos, sin)
-    k_ref = R.apply_rope(qkv[:, Hq * D: (Hq + Hkv) * D].view(T, Hkv, D), cos, sin)
-    v_ref = qkv[:, (Hq + Hkv) * D:].view(T, Hkv, D)
-    scale = float(qkv.abs().max())
-
-    def close(got, want):   # fp32 sums in another order, then ONE bf16 rounding
-        return torch.all((got.float().cpu() - want).abs() <= 2 ** -7 * want.abs() + 2e-6 * scale + 1e-6)
-
-    assert close(qo.view(T, Hq, D), q_ref)
-    written = torch.zeros(nblocks, bs, dtype=torch.bool)
-    for t in range(T):
-        sl = int(slots[t])
-        if sl < 0:
-            continue
-        b, o = sl // bs, sl % bs
-        written[b, o] = True
-        assert close(kc[b, :, o], k_ref[t]) and close(vc[b, :, o], v_ref[t]), t
-    untouched = ~written
-    assert torch.all(torch.isnan(kc.float().cpu().permute(0, 2, 1, 3)[untouched]))
-    assert torch.all(torch.isnan(vc.float().cpu().permute(0, 2, 1, 3)[untouched]))
-    # the unfused pair of entry points on the same operands: identical up to the fp32 summation order
-    qkv_d = torch.zeros(max(T, 8) + 2, N, device="cuda")
-    plan.run(qkv_d, T, cabi.GEMM_STORE_F32, 1)
-    q2 = torch.empty_like(qo)
-    kc2, vc2 = torch.zeros_like(kc), torch.zeros_like(vc)
-    cabi.rope_kv_write(qkv_d, positions.cuda(), slots.cuda(), cs.cuda(), q2, kc2, vc2, T, Hq, Hkv, D, bs)
-    assert close(qo, q2.float().cpu())
-    with pytest.raises(cabi.AtxError, match="head_dim"):
-        cabi.gemm_qkv_rope_kv(plan, T, positions.cuda(), slots.cuda(), cs.cuda(), qo, kc, vc, Hq * 2, Hkv * 2, 64, bs)
+def test_decode_attention_refuses_unsupported_shapes(cabi):
+    """Pages of a multiple of 16 tokens, head_dim 64 | 128, at most 8 query heads per KV head: anything else is
+    refused with the shape spelled out (there is no slower fallback kernel to fall into)."""
+    kc, vc, bt, ks, vs = _paged_case(3, [40], 8, 2, 64)
+    q = _bf16(torch.randn(1, 8 * 64)).cuda()
+    out = torch.empty_like(q)
+    sl = torch.tensor([40], dtype=torch.int32).cuda()
+    with pytest.raises(cabi.AtxError, match="multiple of 16"):
+        cabi.paged_attn_decode(q, kc.cuda(), vc.cuda(), bt.cuda(), sl, out, None, 1, 8, 2, 64, 8, 1, 0.125)
+    with pytest.raises(cabi.AtxError, match="at most 8 query heads"):
+        cabi.paged_attn_decode(q, kc.cuda(), vc.cuda(), bt.cuda(), sl, out, None, 1, 32, 2, 64, 16, 1, 0.125)
