@@ -173,6 +173,8 @@ class EngineConfig:
     enable_cuda_graphs: bool = True
     use_pdl: bool = True
     async_scheduling: bool = True   # launch decode step N+1 before the host has read step N's tokens
+    deterministic: bool = False     # split-K sums in a fixed order (ATX_FLAG_ORDERED): same tokens bit for bit on
+    #                                 every run of the same batches, a few percent slower per decode step
     device: int = 0
     tp_size: int = 1          # tensor-parallel ranks sharing one model (70B); needs torch.distributed NCCL
     tp_rank: int = 0

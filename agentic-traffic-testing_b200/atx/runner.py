@@ -171,7 +171,7 @@ class ModelRunner:
         self._graph_launches: Dict[Tuple[int, int], int] = {}
         self.stream = torch.cuda.Stream(device=dev)   # every launch and copy of this runner
         self._h2d_done = torch.cuda.Event()
-        self.flags = _cabi.FLAG_PDL if e.use_pdl else 0
+        self.flags = (_cabi.FLAG_PDL if e.use_pdl else 0) | (_cabi.FLAG_ORDERED if e.deterministic else 0)
         self.lib.atx_gemm_set_l2_prefetch(int(os.environ.get("ATX_L2_PREFETCH_KB", "0")))
         self.tp_l2_prefetch_kb = int(os.environ.get("ATX_TP_L2_PREFETCH_KB", "0"))
         self.scale = float(m.head_dim) ** -0.5

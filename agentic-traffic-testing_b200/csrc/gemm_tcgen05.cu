@@ -63,7 +63,9 @@ template <int TN>
 __global__ void __launch_bounds__(kGemmThreads)
 gemm_wt_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmX,
                void* __restrict__ out, long long ldo, int T, int N, int kb_total, int kb_per_split,
-               int mode, int w_evict_first, int l2_prefetch_kb, int stages) {
+               int mode_in, int w_evict_first, int l2_prefetch_kb, int stages) {
+    const int mode = mode_in & 0xff;
+    const bool ordered = (mode_in & 0x100) != 0;   // ATX_FLAG_ORDERED: split-K summed in a fixed order (below)
     // `stages` (<= Cfg::kStages) is the ring depth actually used: CTAs with few k-blocks get a smaller
     // shared-memory footprint, so more of them are resident per SM
     using Cfg = GemmCfg<TN>;
@@ -176,9 +178,10 @@ gemm_wt_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
         mbar_wait(accum_bar, 0);
         tc_fence_after();
         pdl_wait();  // `out` may be the residual stream written by the upstream grid
-        const bool nonlinear = mode == ATX_GEMM_SWIGLU_BF16;
+        const bool nonlinear = mode == ATX_GEMM_SWIGLU_BF16 || ordered;
         if (nonlinear && gridDim.z > 1) {
-            // Split-K with a nonlinear epilogue: the gridDim.z CTAs of this tile form ONE thread-block
+            // Split-K with a nonlinear epilogue (or with ATX_FLAG_ORDERED, where the order of the additions must
+            // not depend on timing): the gridDim.z CTAs of this tile form ONE thread-block
             // cluster (launch attribute). CTAs 1.. park their partial accumulator in their own (idle) stage
             // buffers, the leader pulls them through distributed shared memory in a fixed order, folds
             // them into its TMEM accumulator and runs the ordinary SwiGLU epilogue: no workspace, no
@@ -612,7 +615,8 @@ static int launch_gemm(const atx_gemm_plan* p, int ti, void* out, long long ldo,
     int stages = kb_per < Cfg::kStages ? kb_per : Cfg::kStages;
     // the fused-SwiGLU epilogue parks half a tile in the stage buffers: keep them large enough
     // (a whole fp32 tile when the split-K cluster parks partial sums there)
-    if (mode == ATX_GEMM_SWIGLU_BF16) {
+    const bool ordered = (mode & 0x100) != 0;
+    if ((mode & 0xff) == ATX_GEMM_SWIGLU_BF16 || (ordered && zs > 1)) {
         const int need = (TN * (zs > 1 ? kBM : 64) * 4 + Cfg::kStageBytes - 1) / Cfg::kStageBytes;
         if (stages < need) stages = need;
     }
@@ -630,7 +634,7 @@ static int launch_gemm(const atx_gemm_plan* p, int ti, void* out, long long ldo,
         attr[na].val.programmaticStreamSerializationAllowed = 1;
         ++na;
     }
-    if (mode == ATX_GEMM_SWIGLU_BF16 && zs > 1) {  // the K-splits of one tile are one cluster (DSMEM reduction)
+    if (((mode & 0xff) == ATX_GEMM_SWIGLU_BF16 || ordered) && zs > 1) {  // the K-splits of one tile are one cluster (DSMEM reduction)
         attr[na].id = cudaLaunchAttributeClusterDimension;
         attr[na].val.clusterDim.x = 1;
         attr[na].val.clusterDim.y = 1;
@@ -731,6 +735,14 @@ int atx_gemm_run(const atx_gemm_plan* p, void* out, long long ldo, int T, int mo
     ATX_REQUIRE(mode >= ATX_GEMM_STORE_F32 && mode <= ATX_GEMM_SWIGLU_BF16, "atx_gemm_run: bad mode %d", mode);
     ATX_REQUIRE(ldo >= (mode == ATX_GEMM_SWIGLU_BF16 ? p->N / 2 : p->N), "atx_gemm_run: ldo=%lld too small for N=%lld", ldo, p->N);
     ATX_REQUIRE(mode != ATX_GEMM_SWIGLU_BF16 || p->N % 128 == 0, "atx_gemm_run: SWIGLU mode needs N %% 128 == 0");
+    // ATX_FLAG_ORDERED: the K-splits of an ADD are reduced inside a cluster in a fixed order (as for SwiGLU) and ONE CTA
+    // adds each output element, instead of every split racing its red.add: bit-reproducible, a little slower
+    const bool ordered = (flags & ATX_FLAG_ORDERED) && mode == ATX_GEMM_ADD_F32 && T <= 64;
+    if (ordered && splits != 1) {
+        const int want = splits > 0 ? splits : atx_gemm_auto_splits(p->N, p->K, T);
+        splits = 1;
+        while (splits * 2 <= want && splits * 2 <= 8 && (p->K / kBK) % (splits * 2) == 0) splits *= 2;
+    }
     if (splits <= 0) {
         splits = 1;
         if (mode == ATX_GEMM_ADD_F32) splits = atx_gemm_auto_splits(p->N, p->K, T);
@@ -749,9 +761,10 @@ int atx_gemm_run(const atx_gemm_plan* p, void* out, long long ldo, int T, int mo
     const int pdl = (flags & ATX_FLAG_PDL) ? 1 : 0;
     // per-call L2 prefetch depth (k-blocks) in bits 8..15 of flags overrides the process-wide default
     tl_l2_prefetch_kb = ((flags >> 8) & 0xff) ? ((flags >> 8) & 0xff) : g_l2_prefetch_kb;
-    if (T <= 16) return launch_gemm<16>(p, 0, out, ldo, T, mode, splits, pdl, stream);
-    if (T <= 32) return launch_gemm<32>(p, 1, out, ldo, T, mode, splits, pdl, stream);
-    if (T <= 64) return launch_gemm<64>(p, 2, out, ldo, T, mode, splits, pdl, stream);
+    const int kmode = mode | (ordered ? 0x100 : 0);
+    if (T <= 16) return launch_gemm<16>(p, 0, out, ldo, T, kmode, splits, pdl, stream);
+    if (T <= 32) return launch_gemm<32>(p, 1, out, ldo, T, kmode, splits, pdl, stream);
+    if (T <= 64) return launch_gemm<64>(p, 2, out, ldo, T, kmode, splits, pdl, stream);
     // prefill-sized batches: the persistent, warp-specialised kernel (one CTA per SM, two TMEM accumulators)
     ATX_REQUIRE(splits == 1, "atx_gemm_run: split-K is for decode-sized steps (T <= 64); got T=%d splits=%d", T, splits);
     if (T <= 128) return launch_gemm_persistent<128>(p, 3, out, ldo, T, mode, pdl, stream);

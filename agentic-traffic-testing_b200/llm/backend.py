@@ -73,6 +73,7 @@ class B200Backend:
             gpu_memory_utilization=float(gpu_memory_utilization or 0.92),
             block_size=int(os.environ.get("LLM_KV_BLOCK_SIZE") or os.environ.get("VLLM_BLOCK_SIZE") or 16),
             enable_prefix_caching=os.environ.get("LLM_PREFIX_CACHING", "1").lower() in ("1", "true", "yes", "on"),
+            deterministic=os.environ.get("LLM_DETERMINISTIC", "0").lower() in ("1", "true", "yes", "on"),
         )
         self._ecfg = ecfg
         self._vocab = src.config.vocab_size

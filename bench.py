@@ -627,6 +627,7 @@ def main() -> None:
     ap.add_argument("--no-prefix-cache", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--deterministic", action="store_true", help="EngineConfig.deterministic: fixed-order split-K")
     ap.add_argument("--no-multi", action="store_true", help="N > 1: skip the routed-DP and 70B-TP records")
     ap.add_argument("--tp70b-any-n", action="store_true", help="attach the 70B tensor-parallel record at any N > 1 "
                                                                "(default: only at N = 8, BASELINE configs[3])")
@@ -700,7 +701,8 @@ def main() -> None:
         host_pg = dist.new_group(backend="gloo")   # host-side waits that must not occupy a GPU (routed phase)
     mcfg = model_config_by_name(args.model)
     ecfg = EngineConfig(max_model_len=4096, max_num_seqs=12, max_num_batched_tokens=8192,
-                        gpu_memory_utilization=0.90, enable_prefix_caching=not args.no_prefix_cache, device=local)
+                        gpu_memory_utilization=0.90, enable_prefix_caching=not args.no_prefix_cache, device=local,
+                        deterministic=args.deterministic)
     engine = LLMEngine(ModelSource(mcfg, None, 0), ecfg)
     r = engine.runner
     pk = peaks()
@@ -848,6 +850,7 @@ def main() -> None:
             "config": {"workload": WORKLOAD_TEXT,
                        "parallelism": f"dp{world} (independent replicas, no collective)",
                        "prefix_cache": not args.no_prefix_cache, "cuda_graphs": True, "pdl": pdl_on,
+                       "deterministic": bool(args.deterministic),
                        "l2": "inputs larger than L2: 15 GB of weights streamed per decode step vs 126 MB L2",
                        "max_num_seqs": ecfg.max_num_seqs, "max_num_batched_tokens": ecfg.max_num_batched_tokens,
                        "kv_blocks": kv_blocks},

@@ -32,6 +32,10 @@ typedef void* atx_stream_t; /* a cudaStream_t */
 
 /* flags */
 #define ATX_FLAG_PDL 1 /* launch with programmatic dependent launch (stream serialization) */
+/* atx_gemm_run, ATX_GEMM_ADD_F32, T <= 64: sum the K-splits in a FIXED order (the splits of a tile form a
+ * thread-block cluster reduced through distributed shared memory, one CTA adds each output element) instead
+ * of letting every split race its red.add: results are bit-reproducible run to run; splits become 1/2/4/8. */
+#define ATX_FLAG_ORDERED 2
 /* atx_gemm_run only: prefetch this many 16 KB weight slices per CTA into L2 before waiting for the
  * upstream kernel (useful for a GEMM that sits behind a long non-GEMM chain, e.g. o_proj behind attention) */
 #define ATX_FLAG_L2_PREFETCH(kb) (((kb) & 0xff) << 8)

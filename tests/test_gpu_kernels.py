@@ -72,6 +72,31 @@ def test_gemm_matches_fp32_reference(cabi, T, N, K, mode, splits):
     assert ref.shape == got.shape
 
 
+@pytest.mark.parametrize("T,N,K,splits", [(6, 4096, 4096, 0), (6, 6144, 4096, 6), (32, 4096, 14336, 0), (64, 512, 1024, 8),
+                                          (1, 128, 64, 0)])
+def test_gemm_ordered_split_k_is_bit_reproducible(cabi, T, N, K, splits):
+    """ATX_FLAG_ORDERED: the K-splits of an ADD_F32 are summed in a fixed order inside a cluster and one CTA adds
+    each output element, so repeated runs agree bit for bit (plain split-K lets every split race its red.add);
+    the sum itself is checked against the fp64 reference like every other GEMM case."""
+    g = torch.Generator().manual_seed(T + N + K)
+    x = _bf16(torch.randn(T, K, generator=g))
+    w = _bf16(torch.randn(N, K, generator=g) * 0.05)
+    base = torch.randn(T, N, generator=g)
+    xb = torch.zeros(max(T, 8), K, dtype=torch.bfloat16, device="cuda")
+    xb[:T] = x.cuda()
+    plan = cabi.GemmPlan(w.cuda().contiguous(), xb)
+    runs = []
+    for _ in range(4):
+        out = base.cuda().clone()
+        plan.run(out, T, cabi.GEMM_ADD_F32, splits, flags=cabi.FLAG_ORDERED)
+        torch.cuda.synchronize()
+        runs.append(out.cpu())
+    assert all(torch.equal(runs[0], r) for r in runs[1:])
+    want = x.double() @ w.double().T + base.double()
+    scale = x.double().abs() @ w.double().abs().T
+    assert torch.all((runs[0].double() - want).abs() <= 2e-6 * scale + 1e-6)
+
+
 @pytest.mark.parametrize("T,I,K", [(6, 128, 256), (16, 1024, 512), (40, 192, 128), (300, 256, 1024)])
 def test_gemm_fused_swiglu_epilogue(cabi, T, I, K):
     """ATX_GEMM_SWIGLU_BF16: interleaved gate/up rows, act = silu(x Wg^T) * (x Wu^T) in bf16."""

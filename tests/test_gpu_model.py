@@ -217,6 +217,29 @@ def test_async_scheduling_produces_the_same_tokens():
     assert outs[0] == outs[1]
 
 
+def test_deterministic_mode_repeats_itself_bit_for_bit():
+    """EngineConfig.deterministic (LLM_DETERMINISTIC=1): the same burst, run twice on fresh engines through chunked
+    prefill, prefix-cache hits and graph-replayed decode steps, yields bit-identical logits and identical tokens.
+    (Without it the split-K adds race, and a last-bit difference may flip a near-tie: see DESIGN.md section 5.)"""
+    g = torch.Generator().manual_seed(9)
+    shared = torch.randint(0, 1000, (48,), generator=g).tolist()
+    prompts = [shared + torch.randint(0, 1000, (10 + 7 * i,), generator=g).tolist() for i in range(6)]
+    from atx.scheduler import SamplingParams
+
+    outs = []
+    for rep in range(2):
+        eng, _, _ = _engine("tiny128", 21, deterministic=True, enable_cuda_graphs=True, max_num_batched_tokens=128)
+        seqs = [eng.add_request(f"r{i}", p, SamplingParams(temperature=0.0 if i % 2 else 0.7, seed=5 + i, max_tokens=24,
+                                                           ignore_eos=True)) for i, p in enumerate(prompts)]
+        rows = []
+        while eng.has_work():
+            if eng.step():
+                rows.append(eng.runner.logits[:6].clone())
+        outs.append(([s.output_ids for s in seqs], torch.stack(rows).cpu()))
+    assert outs[0][0] == outs[1][0]
+    assert torch.equal(outs[0][1].view(torch.int32), outs[1][1].view(torch.int32))
+
+
 def test_no_cuda_means_loud_failure(monkeypatch):
     from atx.config import EngineConfig, model_config_by_name
     from atx.runner import ModelRunner
