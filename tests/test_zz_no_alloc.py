@@ -54,6 +54,28 @@ def test_static_scratch_decode_matches_caller_scratch_twice_in_a_row():
         assert torch.all((got - ref).abs() <= 2 ** -7 * ref.abs() + 2e-3), float((got - ref).abs().max())
 
 
+def test_static_scratch_decode_matches_the_oracle_directly():
+    """The same entry point against the CPU oracle itself (oracle/llama_ref.py:attention = modeling_llama.py:199-222),
+    so that this file stands on its own: K/V of every sequence are read back through the block table."""
+    from atx import _cabi as cabi
+    from oracle import llama_ref as R
+
+    cabi.load()
+    lens, Hq, Hkv, D, bs = [1, 17, 300, 1153, 64, 999], 32, 8, 128, 16
+    q, kc, vc, bt, sl = _case(404, lens, Hq, Hkv, D)
+    got = torch.full_like(q, float("nan"))
+    cabi.paged_attn_decode_static(q, kc, vc, bt, sl, got, len(lens), Hq, Hkv, D, bs, 8, D ** -0.5)
+    torch.cuda.synchronize()
+    got = got.float().cpu().view(len(lens), Hq, D)
+    for b, L in enumerate(lens):
+        blocks = bt[b, :(L + bs - 1) // bs].long()
+        k = kc[blocks].permute(0, 2, 1, 3).reshape(-1, Hkv, D)[:L].float().cpu()
+        v = vc[blocks].permute(0, 2, 1, 3).reshape(-1, Hkv, D)[:L].float().cpu()
+        want = R.attention(q[b].float().cpu().view(1, Hq, D), k, v, L - 1)[0]
+        # same tolerance as tests/test_gpu_kernels.py::test_paged_decode_attention
+        assert torch.all((got[b] - want).abs() <= 2 ** -7 * want.abs() + 2e-3), (b, L)
+
+
 def test_static_scratch_decode_refuses_oversize_requests_clearly():
     from atx import _cabi as cabi
 
