@@ -489,6 +489,37 @@ def routed_dp_measure(world: int, steps: int, ecfg, model: str = "random:8b:0") 
                     f"processes (one per GPU) over pipes; {world} bursts x 6 requests arrive together per step"}
 
 
+def routed_trace_measure(world: int, device_ecfg, model: str = "random:8b:0") -> dict:
+    """BASELINE configs[2] behind the front door: 4 x `world` synthetic AgentVerse workflows (atx/trace.py: closed
+    loop per task, 5-20 ms think time, N <= 5 concurrent executions per stage, seeded) replayed concurrently against
+    ReplicaPool(world) — every call is routed (prefix affinity, then least outstanding tokens). One untimed replay
+    of other workflows first (graphs, prefix caches start cold for the timed one: fresh ids)."""
+    import dataclasses
+
+    from atx import trace as TR
+    from atx.config import EngineConfig
+    from atx.router import ReplicaPool
+
+    ecfg = dataclasses.replace(EngineConfig(max_model_len=8192, max_num_seqs=32, max_num_batched_tokens=8192,
+                                            gpu_memory_utilization=0.90), device=0)
+    pool = ReplicaPool(model, ecfg, world)
+    try:
+        asyncio.run(TR.replay(pool, TR.generate_tasks(2 * world, seed=1003), seed=1003, id_prefix="w-"))
+        tasks = TR.generate_tasks(4 * world, seed=3)
+        t0 = time.perf_counter()
+        recs = asyncio.run(TR.replay(pool, tasks, seed=3, id_prefix="t-"))
+        wall = time.perf_counter() - t0
+    finally:
+        pool.shutdown()
+    summ = TR.summarize(recs, wall)
+    return {"value": round(summ["tokens_per_s"], 1), "unit": UNIT, "wall_s": round(wall, 2), "tasks": 4 * world,
+            "requests": summ["requests"], "ttft_p50_ms": round(summ["ttft_p50_ms"], 2),
+            "ttft_p95_ms": round(summ["ttft_p95_ms"], 2), "prompt_tokens": summ["prompt_tokens"],
+            "cached_prompt_tokens": summ["cached_prompt_tokens"], "output_tokens": summ["output_tokens"],
+            "workload": "BASELINE configs[2]: synthetic AgentVerse workflows (seeded generator, the reference ships no "
+                        f"traces), {4 * world} concurrent tasks, closed loop, routed over {world} replicas"}
+
+
 # ------------------------------------------------------------------------------------------------------
 def run_other_workload(args, rank, world, local):
     """BASELINE.json configs[2..4]: opt-in workloads (`--workload trace|long|tp70b`). Each prints one JSON
@@ -817,6 +848,10 @@ def main() -> None:
                 routed = routed_dp_measure(world, args.steps, ecfg, "random:%s:0" % args.model)
             except Exception as exc:
                 routed = {"failed": f"{type(exc).__name__}: {exc}"}
+            try:
+                routed["trace_replay"] = routed_trace_measure(world, ecfg, "random:%s:0" % args.model)
+            except Exception as exc:
+                routed["trace_replay"] = {"failed": f"{type(exc).__name__}: {exc}"}
         dist.barrier(group=host_pg)        # ranks 1..N-1 wait on the host: their GPUs belong to the replicas now
         if routed is not None and "value" in routed:
             # the N-GPU end-to-end number is the one with the front door in the path; the per-rank HTTP arm
