@@ -4,7 +4,7 @@
 // attention run on tcgen05 with TMEM accumulators:
 //
 //   S  = Q K^T   M=128 query rows, N=64 keys,  K=128 dims     A=Q (smem, K-major)  B=K  (smem, K-major)
-//   O += P V     M=128 query rows, N=128 dims, K=64 keys      A=P (smem, K-major)  B=V  (smem, MN-major)
+//   O += P V     M=128 query rows, N=128 dims, K=64 keys      A=P (TMEM)           B=V  (smem, MN-major)
 //
 // One CTA = TWO 128-row query tiles (A: rows m0.., B: rows m0+128..) of one head, worked in ping-pong: while the
 // four softmax warps of one tile are busy (TMEM -> registers, mask, max, ex2, P -> smem) the tensor core runs
@@ -17,9 +17,14 @@
 //   warps 2-5   softmax of tile A, warps 6-9 of tile B: ONE thread per query row (no cross-thread exchange):
 //               64 scores from TMEM in one round trip, causal mask on diagonal tiles, running max with a lazy
 //               reference (O in TMEM is rescaled only when some row of the warp grew by more than 2^8), ex2,
-//               P as bf16 into the swizzled A-operand layout, finally O / l -> bf16
+//               P as bf16 pairs written back into the first 32 columns of the S buffer just read (tcgen05.st):
+//               P.V takes its A operand from TMEM, P never crosses shared memory; finally O / l -> bf16
 // TMEM (512 columns): S_A x2, S_B x2 (64 columns each, double-buffered so QK^T(j+1) overlaps softmax(j)),
 // O_A, O_B (128 each). K and V tiles are shared by both query tiles: half the K/V shared-memory traffic per row.
+// Ablations on B200 (S=4 x 8192, 2.2 ms): dropping the exponentials, the maxima, the P hand-over or half of the
+// TMEM reads changes nothing, dropping every K/V load after the first tiles gains 7 %, two threads per row (four
+// softmax warps per scheduler) LOSES 8 %: what is left is the latency of the hand-overs between the tensor pipe and
+// the softmax warps (commit -> mbarrier -> tcgen05.ld behind queued MMAs -> tcgen05.st -> arrive), not a throughput.
 #include "common.cuh"
 
 #include <mutex>
@@ -38,9 +43,8 @@ constexpr int kQAtom = 128 * 128;               // [128 rows x 64 bf16], 128B-sw
 constexpr int kQTile = 2 * kQAtom;              // [128 x 128] bf16
 constexpr int kKVAtom = kTcBN * 128;            // [64 rows x 64 bf16]
 constexpr int kKVTile = 2 * kKVAtom;            // [64 keys x 128 dims] bf16 as two dim-atoms
-constexpr int kPTile = kQAtom;                  // [128 rows x 64 keys] bf16
 constexpr int kKS = 3, kVS = 3;                 // ring depths
-constexpr int kTcSmem = 2 * kQTile + (kKS + kVS) * kKVTile + 2 * kPTile + 1024 + 512;   // + align + barriers
+constexpr int kTcSmem = 2 * kQTile + (kKS + kVS) * kKVTile + 1024 + 512;   // + align + barriers
 
 // MN-major operand ([K rows][64 contiguous N elements] atoms, 128B swizzle): LBO = distance between the
 // N-atoms, SBO = distance between groups of 8 K-rows (cute::UMMA canonical Major-MN SW128 layout).
@@ -70,8 +74,7 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
     uint8_t* sQ = smem;                                   // tile A, tile B
     uint8_t* sK = sQ + 2 * kQTile;                        // kKS stages
     uint8_t* sV = sK + kKS * kKVTile;                     // kVS stages
-    uint8_t* sP = sV + kVS * kKVTile;                     // tile A, tile B
-    uint64_t* bars = reinterpret_cast<uint64_t*>(sP + 2 * kPTile);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(sV + kVS * kKVTile);
     uint64_t* q_full = bars;            // 1
     uint64_t* k_full = bars + 1;        // 4 slots reserved each
     uint64_t* k_empty = bars + 5;
@@ -202,12 +205,12 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
                     if (t == 0 ? j >= nt_a : j >= nt_b) continue;
                     mbar_wait(&p_full[t], j & 1);          // P_t(j) in smem, O_t rescaled, tail rows of V cleared
                     tc_fence_after();
-                    const uint32_t pa = smem_u32(sP + t * kPTile);
+                    const uint32_t pa = tmem_base + t * 128 + (j & 1) * kTcBN;   // P_t(j) lives where S_t(j) was
 #pragma unroll
                     for (int kk = 0; kk < kTcBN / 16; ++kk)
-                        umma_bf16(tmem_base + 256 + t * 128, umma_desc_sw128(pa + kk * 32),
-                                  umma_desc_sw128_mn(va + kk * 16 * 128, kKVAtom), idesc_pv,
-                                  (j > 0 || kk > 0) ? 1u : 0u);
+                        umma_bf16_ts(tmem_base + 256 + t * 128, pa + kk * 8,
+                                     umma_desc_sw128_mn(va + kk * 16 * 128, kKVAtom), idesc_pv,
+                                     (j > 0 || kk > 0) ? 1u : 0u);
                     umma_commit(&o_done[t]);
                 }
                 umma_commit(&v_empty[st]);
@@ -226,7 +229,6 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
         const uint32_t lane_sel = static_cast<uint32_t>(quarter * 32) << 16;
         const uint32_t tmem_S = tmem_base + t * 128 + lane_sel;
         const uint32_t tmem_O = tmem_base + 256 + t * 128 + lane_sel;
-        uint8_t* prow = sP + t * kPTile + row * 128;
         float m_run = -INFINITY, l_run = 0.f;
         for (int j = 0; j < nt; ++j) {
             const int kv0 = j * kTcBN;
@@ -273,16 +275,24 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
                     sv[c][i >> 1] = pack_bf16(p0, p1);
                 }
             l_run = l_run * corr + (ls4[0] + ls4[1]) + (ls4[2] + ls4[3]);
-            // the previous P.V of this tile must have retired before P is overwritten or O is touched
+            // Stay at most one tile ahead of the tensor core: p_full is a one-bit-phase barrier, and a second
+            // arrival round before the issuer has seen the first would leave it waiting for ever. (P.V(j-1) has
+            // retired: also what the O rescale below needs.)
             if (j > 0) mbar_wait(&o_done[t], (j - 1) & 1);
             tc_fence_after();
+            // P as bf16 pairs into the first 32 columns of the S buffer just read (the A operand of P.V comes
+            // from TMEM: nothing of P crosses shared memory)
+            {
+                uint32_t pw[16];
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                const int ch = c * 2;  // the two 16-byte chunks of these 16 keys
-                *reinterpret_cast<uint4*>(prow + ((ch ^ (row & 7)) << 4)) =
-                    make_uint4(sv[c][0], sv[c][1], sv[c][2], sv[c][3]);
-                *reinterpret_cast<uint4*>(prow + (((ch + 1) ^ (row & 7)) << 4)) =
-                    make_uint4(sv[c][4], sv[c][5], sv[c][6], sv[c][7]);
+                for (int hlf = 0; hlf < 2; ++hlf) {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        pw[i] = sv[2 * hlf][i];
+                        pw[8 + i] = sv[2 * hlf + 1][i];
+                    }
+                    tmem_st16(tmem_S + (j & 1) * kTcBN + hlf * 16, pw);
+                }
             }
             // rescale this row of O only if some row of the warp moved its maximum
             if (j > 0 && moved) {
@@ -295,8 +305,8 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
                     for (int i = 0; i < 16; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) * corr);
                     tmem_st16(tmem_O + c, v);
                 }
-                tmem_st_wait();
             }
+            tmem_st_wait();
             // keys past the context in the last tile: their V rows are stale page contents or never-loaded
             // shared memory; P is 0 there but 0 * NaN would poison O, so clear those rows (both dim-atoms)
             if (kv0 + kTcBN > ctx) {
@@ -310,8 +320,8 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
                         *reinterpret_cast<uint4*>(vrow + kKVAtom + i * 16) = make_uint4(0, 0, 0, 0);
                     }
                 }
+                fence_proxy_async();   // generic-proxy smem writes (cleared V rows) -> visible to the tensor core
             }
-            fence_proxy_async();   // generic-proxy smem writes (P, cleared V rows) -> visible to the tensor core
             tc_fence_before();
             mbar_arrive(&p_full[t]);
         }
