@@ -30,7 +30,7 @@ EXPORTS = [
     "atx_reduce_scatter_rmsnorm_all_gather", "atx_allreduce_add_rmsnorm_ll",
     "atx_paged_attn_decode_workspace_bytes", "atx_paged_attn_decode", "atx_paged_attn_prefill",
     "atx_paged_attn_decode_static", "atx_paged_attn_decode_static_capacity",
-    "atx_sample",
+    "atx_sample", "atx_sample_shard", "atx_sample_merge",
 ]
 
 
@@ -93,6 +93,8 @@ def load() -> C.CDLL:
     lib.atx_paged_attn_prefill.argtypes = [vp, vp, vp, vp, vp, vp, vp, i32, i32, i64, i64, i32, i32, i32, i32, i32, f32,
                                            i32, vp]
     lib.atx_sample.argtypes = [vp, i64, vp, vp, vp, vp, vp, i32, i32, i32, vp]
+    lib.atx_sample_shard.argtypes = [vp, i64, i32, vp, vp, vp, vp, i32, i32, i32, vp]
+    lib.atx_sample_merge.argtypes = [vp, i32, i32, vp, i32, vp]
     for name in EXPORTS:  # fail at load time, not at first use, if the build is stale
         getattr(lib, name)
     _lib = lib
@@ -245,3 +247,18 @@ def sample(logits: torch.Tensor, out_ids: torch.Tensor, B: int, V: int, temperat
     assert steps is None or steps.dtype == torch.int32
     _check(load().atx_sample(logits.data_ptr(), logits.stride(0), _p(temperature), _p(top_p), _p(seeds), _p(steps),
                              out_ids.data_ptr(), B, V, flags, _stream()))
+
+
+def sample_shard(logits: torch.Tensor, idx_offset: int, pairs: torch.Tensor, B: int, V_local: int,
+                 temperature: Optional[torch.Tensor] = None, seeds: Optional[torch.Tensor] = None,
+                 steps: Optional[torch.Tensor] = None, flags: int = 0) -> None:
+    _dev(logits, pairs, temperature, seeds, steps)
+    assert logits.dtype == torch.float32 and pairs.dtype == torch.float32 and pairs.numel() >= 2 * B
+    _check(load().atx_sample_shard(logits.data_ptr(), logits.stride(0), idx_offset, _p(temperature), _p(seeds), _p(steps),
+                                   pairs.data_ptr(), B, V_local, flags, _stream()))
+
+
+def sample_merge(pairs: torch.Tensor, world: int, B: int, out_ids: torch.Tensor, flags: int = 0) -> None:
+    _dev(pairs, out_ids)
+    assert pairs.dtype == torch.float32 and pairs.numel() >= 2 * world * B and out_ids.dtype == torch.int32
+    _check(load().atx_sample_merge(pairs.data_ptr(), world, B, out_ids.data_ptr(), flags, _stream()))

@@ -101,6 +101,9 @@ class ModelRunner:
             self.xn2 = self.xn    # input of gate_up; a buffer of its own only under the low-latency all-reduce
         self.logits = torch.zeros(S, V, dtype=f32, device=dev)
         self.out_ids = torch.zeros(S, dtype=i32, device=dev)
+        if tp > 1:   # (score, global index) of this rank's vocabulary shard per row, and every rank's after the exchange
+            self.pairs = torch.zeros(S, 2, dtype=f32, device=dev)
+            self.pairs_all = torch.zeros(tp, S, 2, dtype=f32, device=dev)
         self.out_host = [torch.zeros(S, dtype=i32).pin_memory() for _ in range(2)]  # ping-pong: one step may be in flight
         self._out_events = [torch.cuda.Event(), torch.cuda.Event()]
         self._out_flip = 0
@@ -167,8 +170,8 @@ class ModelRunner:
         self.k_cache = torch.zeros(L, nb, Hkv, self.bs, D, dtype=bf, device=dev)
         self.v_cache = torch.zeros(L, nb, Hkv, self.bs, D, dtype=bf, device=dev)
 
-        self._graphs: Dict[Tuple[int, int], torch.cuda.CUDAGraph] = {}
-        self._graph_launches: Dict[Tuple[int, int], int] = {}
+        self._graphs: Dict[Tuple[int, int, bool], torch.cuda.CUDAGraph] = {}
+        self._graph_launches: Dict[Tuple[int, int, bool], int] = {}
         self.stream = torch.cuda.Stream(device=dev)   # every launch and copy of this runner
         self._h2d_done = torch.cuda.Event()
         self.flags = (_cabi.FLAG_PDL if e.use_pdl else 0) | (_cabi.FLAG_ORDERED if e.deterministic else 0)
@@ -187,7 +190,8 @@ class ModelRunner:
         if rc != 0:
             raise _cabi.AtxError(f"atx error {rc}: {self.lib.atx_last_error().decode()}")
 
-    def _forward(self, T: int, n_dec: int, dec_splits: int, n_pf: int, max_q: int, n_rows: int) -> int:
+    def _forward(self, T: int, n_dec: int, dec_splits: int, n_pf: int, max_q: int, n_rows: int,
+                 whole_rows: bool = False) -> int:
         """Issue every kernel of one step on the current stream. Returns the launch count.
 
         Tensor parallel (tp > 1, Megatron split: q/k/v/gate/up by output features = heads, o/down by
@@ -195,8 +199,11 @@ class ModelRunner:
         all-reduce, the residual add and the following RMSNorm are one kernel over NVLink peer memory
         (atx_allreduce_add_rmsnorm, ping-pong symmetric buffers); prefill-sized steps use NCCL's ring and
         fold the reduced partial into the residual inside the RMSNorm kernel (`add`). The LM head is
-        vocabulary-parallel: each rank fills its column slice of a zeroed logits buffer and one NCCL
-        all-reduce assembles the rows, so every rank samples the same token."""
+        vocabulary-parallel: each rank computes its column slice of the logits, reduces every row of it to one
+        (score, global index) pair (atx_sample_shard: arg-max, or Gumbel-max keyed by the global index), the ranks
+        exchange the pairs (8 bytes per row and rank, one NCCL all-gather) and pick the best (atx_sample_merge):
+        the same token on every rank, and the token the unsharded sampler draws. Only when a request asks for a
+        nucleus (top_p < 1: `whole_rows`) are the rows themselves assembled (all-reduce of a zero-filled buffer)."""
         lib, m, w, ck = self.lib, self.m, self.w, self._ck
         st = torch.cuda.current_stream().cuda_stream
         fl = self.flags
@@ -285,6 +292,19 @@ class ModelRunner:
             project(p_down)
         if n_rows:
             norm(w.norm.data_ptr(), self.xl.data_ptr(), rows_ptr=dp["rows"], rows_n=n_rows)
+            if tp > 1 and not whole_rows:
+                import torch.distributed as dist
+
+                Vl = V // tp
+                shard = self.logits.data_ptr() + 4 * Vl * self.tp_rank       # this rank's columns of the [S, V] buffer
+                ck(lib.atx_gemm_run(self.plan_lm._h, shard, V, n_rows, _cabi.GEMM_STORE_F32, 1, fl, st))
+                ck(lib.atx_sample_shard(shard, V, Vl * self.tp_rank, dp["temps"], dp["seeds"], dp["steps"],
+                                        self.pairs.data_ptr(), n_rows, Vl, fl, st))
+                dist.all_gather_into_tensor(self.pairs_all, self.pairs, group=self.tp_group)
+                self.allreduce_calls += 1
+                ck(lib.atx_sample_merge(self.pairs_all.data_ptr(), tp, self.pairs.shape[0], self.out_ids.data_ptr(), fl,
+                                        st))
+                return n + 3
             if tp > 1:
                 Vl = V // tp
                 self.logits[:n_rows].zero_()
@@ -546,19 +566,20 @@ class ModelRunner:
         self._h2d_done.record()
 
         splits = self.decode_splits(B, max_len)
+        whole_rows = self.tp > 1 and any(c.seq.params.top_p < 1.0 and c.seq.params.temperature > 0.0 for c in sampling)
         ev0 = None
         if self.step_events is not None:
             ev0 = torch.cuda.Event(enable_timing=True)
             ev0.record()
         if use_graph:
-            key = (B, splits)
+            key = (B, splits, whole_rows)
             g = self._graphs.get(key)
             if g is None:
-                g = self._capture(B, splits)
+                g = self._capture(B, splits, whole_rows)
             g.replay()
             self.launches_last_step = self._graph_launches[key]
         else:
-            self.launches_last_step = self._forward(T, B, splits, n_pf, max_q, n_rows)
+            self.launches_last_step = self._forward(T, B, splits, n_pf, max_q, n_rows, whole_rows)
         self.kernel_launches += self.launches_last_step
         if ev0 is not None:
             ev1 = torch.cuda.Event(enable_timing=True)
@@ -575,21 +596,21 @@ class ModelRunner:
             ev.record()
         return (sampling, n_dec, B, buf, ev)
 
-    def _capture(self, B: int, splits: int) -> torch.cuda.CUDAGraph:
+    def _capture(self, B: int, splits: int, whole_rows: bool = False) -> torch.cuda.CUDAGraph:
         """Capture one decode step for batch bucket B. Inputs already sit in dbuf; the warm-up run
         writes the same K/V slots and logits the replay will write again, so it is harmless."""
         torch.cuda.current_stream().synchronize()
         s = torch.cuda.Stream(device=self.dev)
         s.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(s):
-            self._forward(B, B, splits, 0, 0, B)  # warm-up: sets func attributes outside capture
+            self._forward(B, B, splits, 0, 0, B, whole_rows)  # warm-up: sets func attributes outside capture
         torch.cuda.current_stream().wait_stream(s)
         torch.cuda.synchronize(self.dev)
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g, stream=s, capture_error_mode="thread_local"):
-            n = self._forward(B, B, splits, 0, 0, B)
-        self._graphs[(B, splits)] = g
-        self._graph_launches[(B, splits)] = n
+            n = self._forward(B, B, splits, 0, 0, B, whole_rows)
+        self._graphs[(B, splits, whole_rows)] = g
+        self._graph_launches[(B, splits, whole_rows)] = n
         return g
 
     def close(self) -> None:

@@ -85,10 +85,16 @@ __device__ __forceinline__ void for_each_logit(const float* __restrict__ row, in
     }
 }
 
+// With `pairs` set the row is one SHARD of a vocabulary-parallel row (columns [idx_offset, idx_offset + V) of the
+// full row): instead of a token id the kernel emits the shard's best (score, global index) pair, score = the
+// logit (greedy) or logit / T + Gumbel noise keyed by the GLOBAL index; the arg-max over the shards' pairs
+// (sample_merge_kernel) is then exactly the token the unsharded kernel draws. No nucleus here (it needs the sum over
+// the whole row): the caller assembles full rows when a request asks for top_p < 1.
 __global__ void __launch_bounds__(kSampThreads)
 sample_kernel(const float* __restrict__ logits, long long ldl, const float* __restrict__ temperature,
               const float* __restrict__ top_p, const unsigned long long* __restrict__ seeds,
-              const int* __restrict__ steps, int* __restrict__ out_ids, int V) {
+              const int* __restrict__ steps, int* __restrict__ out_ids, int V, int idx_offset,
+              float2* __restrict__ pairs) {
     __shared__ ArgMax sh_am[kSampThreads / 32];
     __shared__ float sh_f[kSampThreads / 32];
     pdl_launch_dependents();
@@ -103,12 +109,15 @@ sample_kernel(const float* __restrict__ logits, long long ldl, const float* __re
     for_each_logit(row, V, vec, [&](float l, int i) { am = better(am, ArgMax{l, i}); });
     am = block_argmax(am, sh_am);
     if (!(T > 0.f)) {
-        if (threadIdx.x == 0) out_ids[b] = am.i;
+        if (threadIdx.x == 0) {
+            if (pairs) pairs[b] = make_float2(am.v, __int_as_float(am.i + idx_offset));
+            else out_ids[b] = am.i;
+        }
         return;
     }
     const float inv_t = 1.f / T;
     const float lmax = am.v;
-    const float P = top_p ? top_p[b] : 1.f;
+    const float P = (top_p && !pairs) ? top_p[b] : 1.f;
 
     float thr = 0.f;  // keep e_i >= thr, e_i = exp((l_i - lmax) / T) in (0, 1]
     if (P < 1.f) {
@@ -139,10 +148,27 @@ sample_kernel(const float* __restrict__ logits, long long ldl, const float* __re
     ArgMax best = {-INFINITY, 0x7fffffff};
     for_each_logit(row, V, vec, [&](float l, int i) {
         if (thr > 0.f && !(expf((l - lmax) * inv_t) >= thr)) return;
-        best = better(best, ArgMax{l * inv_t + gumbel(key, static_cast<uint32_t>(i)), i});
+        best = better(best, ArgMax{l * inv_t + gumbel(key, static_cast<uint32_t>(i + idx_offset)), i});
     });
     best = block_argmax(best, sh_am);
-    if (threadIdx.x == 0) out_ids[b] = best.i < V ? best.i : am.i;
+    if (threadIdx.x == 0) {
+        if (pairs) pairs[b] = make_float2(best.v, __int_as_float((best.i < V ? best.i : am.i) + idx_offset));
+        else out_ids[b] = best.i < V ? best.i : am.i;
+    }
+}
+
+// out_ids[b] = index of the best pair among the `world` shards of row b (highest score, lowest index on ties).
+__global__ void sample_merge_kernel(const float2* __restrict__ pairs, int world, int B, int* __restrict__ out_ids) {
+    pdl_launch_dependents();
+    pdl_wait();
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    ArgMax best = {-INFINITY, 0x7fffffff};
+    for (int r = 0; r < world; ++r) {
+        const float2 p = pairs[static_cast<long long>(r) * B + b];
+        best = better(best, ArgMax{p.x, __float_as_int(p.y)});
+    }
+    out_ids[b] = best.i;
 }
 
 }  // namespace atx
@@ -165,7 +191,43 @@ int atx_sample(const float* logits, long long ldl, const float* temperature, con
     cfg.gridDim = dim3(static_cast<unsigned>(B));
     cfg.blockDim = dim3(kSampThreads);
     cfg.stream = reinterpret_cast<cudaStream_t>(stream);
-    ATX_CUDA(cudaLaunchKernelEx(&cfg, sample_kernel, logits, ldl, temperature, top_p, seeds, steps, out_ids, V));
+    ATX_CUDA(cudaLaunchKernelEx(&cfg, sample_kernel, logits, ldl, temperature, top_p, seeds, steps, out_ids, V, 0,
+                                static_cast<float2*>(nullptr)));
+    return ATX_OK;
+}
+
+int atx_sample_shard(const float* logits, long long ldl, int idx_offset, const float* temperature,
+                     const unsigned long long* seeds, const int* steps, void* pairs, int B, int V_local, int flags,
+                     atx_stream_t stream) {
+    ATX_REQUIRE(logits && pairs, "atx_sample_shard: null pointer");
+    ATX_REQUIRE(B > 0 && V_local > 0 && ldl >= V_local && idx_offset >= 0,
+                "atx_sample_shard: bad shape B=%d V_local=%d ldl=%lld offset=%d", B, V_local, ldl, idx_offset);
+    cudaLaunchConfig_t cfg = {};
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = (flags & ATX_FLAG_PDL) ? 1 : 0;
+    cfg.gridDim = dim3(static_cast<unsigned>(B));
+    cfg.blockDim = dim3(kSampThreads);
+    cfg.stream = reinterpret_cast<cudaStream_t>(stream);
+    ATX_CUDA(cudaLaunchKernelEx(&cfg, sample_kernel, logits, ldl, temperature, static_cast<const float*>(nullptr), seeds,
+                                steps, static_cast<int*>(nullptr), V_local, idx_offset, static_cast<float2*>(pairs)));
+    return ATX_OK;
+}
+
+int atx_sample_merge(const void* pairs, int world, int B, int* out_ids, int flags, atx_stream_t stream) {
+    ATX_REQUIRE(pairs && out_ids && world > 0 && B > 0, "atx_sample_merge: bad arguments");
+    cudaLaunchConfig_t cfg = {};
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = (flags & ATX_FLAG_PDL) ? 1 : 0;
+    cfg.gridDim = dim3(static_cast<unsigned>((B + 127) / 128));
+    cfg.blockDim = dim3(128);
+    cfg.stream = reinterpret_cast<cudaStream_t>(stream);
+    ATX_CUDA(cudaLaunchKernelEx(&cfg, sample_merge_kernel, static_cast<const float2*>(pairs), world, B, out_ids));
     return ATX_OK;
 }
 

@@ -203,6 +203,18 @@ int atx_sample(const float* logits, long long ldl, const float* temperature, con
                const unsigned long long* seeds, const int* steps, int* out_ids, int B, int V, int flags,
                atx_stream_t stream);
 
+/* Vocabulary-parallel form of the above (tensor parallelism: each rank holds V / world columns of every logits row,
+ * the LM head being sharded by vocabulary): atx_sample_shard reduces this rank's shard of each row to ONE
+ * (score, global index) pair — the logit for greedy rows, logit / T + Gumbel noise keyed by the GLOBAL token index
+ * otherwise — and atx_sample_merge, given the `world` shards' pairs ([world][B] float2: score, index bits), picks the
+ * best (lowest index on ties): exactly the token atx_sample draws from the assembled row, with 8 bytes per row and
+ * rank exchanged instead of the row itself. Replaces the logits all-gather vLLM performs before its sampler under
+ * tensor parallelism (reached through llm/serve_llm.py:374-379). No top-p here (it needs the whole row's sum). */
+int atx_sample_shard(const float* logits, long long ldl, int idx_offset, const float* temperature,
+                     const unsigned long long* seeds, const int* steps, void* pairs, int B, int V_local, int flags,
+                     atx_stream_t stream);
+int atx_sample_merge(const void* pairs, int world, int B, int* out_ids, int flags, atx_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -393,6 +393,35 @@ def test_temperature_sampling_matches_oracle_stream(cabi):
         assert sc[ids[b]] >= sc.max() - 1e-4, b
 
 
+@pytest.mark.parametrize("world", [2, 8])
+def test_vocabulary_parallel_sampling_equals_the_unsharded_sampler(cabi, world):
+    """atx_sample_shard on each vocabulary shard + atx_sample_merge over the shards' (score, index) pairs draws
+    exactly the token atx_sample draws from the whole row: greedy rows (with a tie that straddles two shards: the
+    lowest index wins) and temperature rows (Gumbel noise keyed by the global index)."""
+    V, B = 128256, 12
+    Vl = V // world
+    g = torch.Generator().manual_seed(31 + world)
+    logits = torch.randn(B, V, generator=g) * 2
+    logits[1, Vl - 1] = logits[1, Vl] = 40.0           # tie across the boundary of shards 0 and 1
+    logits[2, V - 1] = 45.0
+    temps = torch.tensor([0.0, 0.0, 0.0] + [0.2, 0.7, 1.0] * 3)
+    seeds = torch.arange(B, dtype=torch.int64) * 104729 + (1 << 41)
+    steps = torch.arange(B, dtype=torch.int32) * 3
+    d, temps, seeds, steps = logits.cuda(), temps.cuda(), seeds.cuda(), steps.cuda()
+    want = torch.empty(B, dtype=torch.int32, device="cuda")
+    cabi.sample(d, want, B, V, temps, None, seeds, steps)
+    pairs = torch.zeros(world, B, 2, device="cuda")
+    for r in range(world):
+        shard = d[:, r * Vl:(r + 1) * Vl]                # a strided view: ldl = V, as in the engine
+        cabi._check(cabi.load().atx_sample_shard(shard.data_ptr(), V, r * Vl, temps.data_ptr(), seeds.data_ptr(),
+                                                  steps.data_ptr(), pairs[r].data_ptr(), B, Vl, 0,
+                                                  torch.cuda.current_stream().cuda_stream))
+    got = torch.empty(B, dtype=torch.int32, device="cuda")
+    cabi.sample_merge(pairs, world, B, got)
+    assert got.cpu().tolist() == want.cpu().tolist()
+    assert got[1].item() == Vl - 1 and got[2].item() == V - 1
+
+
 def test_temperature_sampling_distribution(cabi):
     """Chi-square style check of the draw against softmax(l / T) on a small vocabulary."""
     V, N = 8, 4096

@@ -41,10 +41,14 @@ def _rank(rank, world, port, graphs, mode, q, temperature=0.0, n_new=16):
         seq = eng.add_request("tp", g["prompt"].tolist(), SamplingParams(temperature=temperature, max_tokens=n_new,
                                                                          ignore_eos=True))
         eng.step()
-        first = eng.runner.logits[0].float().cpu().numpy()
+        # the LM head is sharded by vocabulary and the ranks exchange (score, index) pairs, not rows: each rank
+        # holds (and checks) its own columns of the logits
+        Vl = mcfg.vocab_size // world
+        cols = slice(rank * Vl, (rank + 1) * Vl)
+        first = eng.runner.logits[0, cols].float().cpu().numpy()
         while eng.has_work():
             eng.step()
-        q.put((rank, float(np.abs(first - g["logits_last"]).max()), seq.output_ids, eng.runner.allreduce_calls,
+        q.put((rank, float(np.abs(first - g["logits_last"][cols]).max()), seq.output_ids, eng.runner.allreduce_calls,
                eng.runner.fused_ar))
         eng.runner.close()
     finally:
