@@ -288,12 +288,10 @@ gemm_wt_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
                         if (t < T) o[static_cast<long long>(t) * ldo + n] = __uint_as_float(v[j]);
                     }
                 } else if (mode == ATX_GEMM_ADD_F32) {
-                    float* o = reinterpret_cast<float*>(out);
+                    // parked in shared memory (token-major) and added below, four consecutive outputs at a time
+                    float* part = reinterpret_cast<float*>(smem);  // [TN][128]: the stage buffers are idle now
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) {
-                        const int t = t0 + c + j;
-                        if (t < T) atomicAdd(o + static_cast<long long>(t) * ldo + n, __uint_as_float(v[j]));
-                    }
+                    for (int j = 0; j < 16; ++j) part[(c + j) * kBM + warp * 32 + lane] = __uint_as_float(v[j]);
                 } else {
                     __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out);
 #pragma unroll
@@ -302,6 +300,34 @@ gemm_wt_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
                         if (t < T)
                             o[static_cast<long long>(t) * ldo + n] = __float2bfloat16_rn(__uint_as_float(v[j]));
                     }
+                }
+            }
+        }
+        if (mode == ATX_GEMM_ADD_F32) {
+            // The split-K / residual add as 16-byte reductions: a thread's accumulator lane is ONE output column, so
+            // added straight from registers every value is its own red.add (with T = 32 and 26 K-splits the qkv GEMM
+            // of a 70B tensor-parallel shard issues a million of them onto 40 K addresses: the L2's atomic units,
+            // not HBM, set its time). Through shared memory a thread owns four consecutive columns of a token.
+            __syncthreads();
+            const float* part = reinterpret_cast<const float*>(smem);
+            float* o = reinterpret_cast<float*>(out);
+            const int rows = min(TN, T - t0);
+            const bool vec = (N & 3) == 0 && (ldo & 3) == 0 && (reinterpret_cast<uintptr_t>(o) & 15) == 0;
+            for (int idx = threadIdx.x; idx < rows * (kBM / 4); idx += kGemmThreads) {
+                const int tt = idx / (kBM / 4), n4 = (idx % (kBM / 4)) * 4;
+                const int nn = n0 + n4;
+                if (nn >= N) continue;
+                const float4 a = *reinterpret_cast<const float4*>(part + tt * kBM + n4);
+                float* dst = o + static_cast<long long>(t0 + tt) * ldo + nn;
+                if (vec) {
+                    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "f"(a.x), "f"(a.y), "f"(a.z),
+                                 "f"(a.w)
+                                 : "memory");
+                } else {
+                    atomicAdd(dst, a.x);
+                    if (nn + 1 < N) atomicAdd(dst + 1, a.y);
+                    if (nn + 2 < N) atomicAdd(dst + 2, a.z);
+                    if (nn + 3 < N) atomicAdd(dst + 3, a.w);
                 }
             }
         }
@@ -616,8 +642,11 @@ static int launch_gemm(const atx_gemm_plan* p, int ti, void* out, long long ldo,
     // the fused-SwiGLU epilogue parks half a tile in the stage buffers: keep them large enough
     // (a whole fp32 tile when the split-K cluster parks partial sums there)
     const bool ordered = (mode & 0x100) != 0;
-    if ((mode & 0xff) == ATX_GEMM_SWIGLU_BF16 || (ordered && zs > 1)) {
-        const int need = (TN * (zs > 1 ? kBM : 64) * 4 + Cfg::kStageBytes - 1) / Cfg::kStageBytes;
+    if ((mode & 0xff) == ATX_GEMM_SWIGLU_BF16 || (mode & 0xff) == ATX_GEMM_ADD_F32) {
+        // epilogues that park the tile in the (idle) stage buffers: half a tile for SwiGLU, a whole fp32 tile for the
+        // split-K cluster reduction and for the 16-byte adds
+        const bool whole = zs > 1 || (mode & 0xff) == ATX_GEMM_ADD_F32;
+        const int need = (TN * (whole ? kBM : 64) * 4 + Cfg::kStageBytes - 1) / Cfg::kStageBytes;
         if (stages < need) stages = need;
     }
     const int smem_bytes = stages * Cfg::kStageBytes + 1024 + 256;
