@@ -6,25 +6,33 @@
 //   S  = Q K^T   M=128 query rows, N=64 keys,  K=128 dims     A=Q (smem, K-major)  B=K  (smem, K-major)
 //   O += P V     M=128 query rows, N=128 dims, K=64 keys      A=P (TMEM)           B=V  (smem, MN-major)
 //
-// One CTA = TWO 128-row query tiles (A: rows m0.., B: rows m0+128..) of one head, worked in ping-pong: while the
-// four softmax warps of one tile are busy (TMEM -> registers, mask, max, ex2, P -> smem) the tensor core runs
-// the other tile's QK^T / PV, so neither side idles on the other. (The first version had one tile per CTA with
-// two threads per row; ncu showed the tensor pipe 31 % active and the softmax warps, with two block barriers
-// and a shared-memory exchange per tile, as the critical path: profiles/r01n.) Roles:
-//   warp 0      TMA producer: Q_A, Q_B once; K and V in 64-key tiles (four pages; a page of one KV head is
-//               16 rows x 256 B, two 128B-swizzled boxes), 3-deep rings, K one tile ahead of V
-//   warp 1      the single MMA-issuing thread: QK_A(j+1), QK_B(j+1), then PV_A(j), PV_B(j) as their P arrives
+// One CTA = TWO 128-row query tiles (A: rows m0.., B: rows m0+128..) of one head; K/V arrive in 128-key tiles and are
+// handed between the tensor pipe and the softmax warps in 64-key HALVES, which gives FOUR independent chains
+// (tile A | B) x (keys 0-63 | 64-127):   [wait P_c(j)]  P.V_c(j)  QK_c(j+1)  ->  S_c(j+1)  ->  softmax  ->  P_c(j+1)
+// While the softmax warps of a tile work on one half, the tensor pipe runs the other half and the other tile. Roles:
+//   warp 0      TMA producer: Q_A, Q_B once; K and V in 128-key tiles (eight pages; a page of one KV head is
+//               16 rows x 256 B, two 128B-swizzled boxes, lane p loads page p), 2-deep rings, K one tile ahead of V
+//   warp 1      the single MMA-issuing thread, chains in the fixed rotation A_lo, B_lo, A_hi, B_hi. QK_c(j+1)
+//               overwrites exactly the TMEM columns P_c(j) sits in: tcgen05.mma execute in issue order, so that is
+//               safe once P.V_c(j) has been issued, and S needs no second buffer
 //   warps 2-5   softmax of tile A, warps 6-9 of tile B: ONE thread per query row (no cross-thread exchange):
 //               64 scores from TMEM in one round trip, causal mask on diagonal tiles, running max with a lazy
-//               reference (O in TMEM is rescaled only when some row of the warp grew by more than 2^8), ex2,
-//               P as bf16 pairs written back into the first 32 columns of the S buffer just read (tcgen05.st):
-//               P.V takes its A operand from TMEM, P never crosses shared memory; finally O / l -> bf16
-// TMEM (512 columns): S_A x2, S_B x2 (64 columns each, double-buffered so QK^T(j+1) overlaps softmax(j)),
-// O_A, O_B (128 each). K and V tiles are shared by both query tiles: half the K/V shared-memory traffic per row.
-// Ablations on B200 (S=4 x 8192, 2.2 ms): dropping the exponentials, the maxima, the P hand-over or half of the
-// TMEM reads changes nothing, dropping every K/V load after the first tiles gains 7 %, two threads per row (four
-// softmax warps per scheduler) LOSES 8 %: what is left is the latency of the hand-overs between the tensor pipe and
-// the softmax warps (commit -> mbarrier -> tcgen05.ld behind queued MMAs -> tcgen05.st -> arrive), not a throughput.
+//               reference (O in TMEM is rescaled only when some row of the warp grew by more than 2^8; then the
+//               P.V of the other half, possibly still accumulating, is waited for first), ex2 with packed
+//               FFMA2 / FADD2 arithmetic around it, P as bf16 pairs written back into the first 32 columns of the
+//               half just read (tcgen05.st): P.V takes its A operand from TMEM, P never crosses shared memory;
+//               finally O / l -> bf16
+// TMEM (512 columns): S_A, S_B (128 each = two 64-column halves), O_A, O_B (128 each). K and V tiles are shared by
+// both query tiles. Grid: 1-D, the G heads of a KV group fastest, then the query tile pairs of a (sequence, KV head)
+// from the LAST (most keys) to the first: the launch ends on short CTAs and the resident CTAs share K/V in L2.
+// History (profiles/r01n, r02j, r02zc): one tile per CTA with two threads per row: tensor pipe 31 % active; two
+// tiles with 64-key tiles and double-buffered S: 47.5 % (each P store waited for the previous P.V of its tile: a
+// ~1500-cycle serial chain per 64 keys); 128-key tiles, two chains: 57 % (softmax of a tile 2200 cycles against a
+// 1100-cycle MMA batch); this version: 61 %, 1205 TFLOP/s causal at S=4 x 8192. What is left: the MUFU unit
+// retires 4 ex2 per cycle and scheduler (XU pipe 62 % busy), the softmax warps wait 34 % of their time for S, and a
+// pure MMA + TMA stream of this operand mix without any hand-over reaches 1555 TFLOP/s at the 1.64 GHz the SMs hold.
+// Tried and dropped here: a second MMA-issuing thread (1121), a polynomial exp2 for a share of the scores (slower at
+// every share: it costs more issue slots than the MUFU it frees), 128 threads arriving vs one per warp (same).
 #include "common.cuh"
 
 #include <mutex>
@@ -35,15 +43,16 @@
 namespace atx {
 
 constexpr int kTcBM = 128;        // query rows per tile (two tiles per CTA)
-constexpr int kTcBN = 64;         // keys per tile
+constexpr int kTcBN = 128;        // keys per K/V tile
+constexpr int kTcHalf = 64;       // keys per softmax / MMA hand-over (half a tile)
 constexpr int kTcD = 128;
 constexpr int kTcThreads = 320;   // TMA warp, MMA warp, 4 + 4 softmax warps
 constexpr int kTcPage = 16;
 constexpr int kQAtom = 128 * 128;               // [128 rows x 64 bf16], 128B-swizzled: one K-atom of Q (or of P)
 constexpr int kQTile = 2 * kQAtom;              // [128 x 128] bf16
-constexpr int kKVAtom = kTcBN * 128;            // [64 rows x 64 bf16]
-constexpr int kKVTile = 2 * kKVAtom;            // [64 keys x 128 dims] bf16 as two dim-atoms
-constexpr int kKS = 3, kVS = 3;                 // ring depths
+constexpr int kKVAtom = kTcBN * 128;            // [128 keys x 64 bf16]
+constexpr int kKVTile = 2 * kKVAtom;            // [128 keys x 128 dims] bf16 as two dim-atoms
+constexpr int kKS = 2, kVS = 2;                 // ring depths
 constexpr int kTcSmem = 2 * kQTile + (kKS + kVS) * kKVTile + 1024 + 512;   // + align + barriers
 
 // MN-major operand ([K rows][64 contiguous N elements] atoms, 128B swizzle): LBO = distance between the
@@ -62,12 +71,33 @@ __device__ __forceinline__ float ex2_approx(float x) {  // one MUFU op; 2^-inf =
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
+// Packed fp32 pairs (FFMA2 / FADD2 on sm_100): the softmax warps are issue-bound, two scores per instruction.
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
+    f32x2 v;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(v) : "f"(lo), "f"(hi));
+    return v;
+}
+__device__ __forceinline__ void unpack2(f32x2 v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+    f32x2 d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
+    f32x2 d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
 
 __global__ void __launch_bounds__(kTcThreads, 1)
 attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                        const __grid_constant__ CUtensorMap tmV, const int* __restrict__ block_table,
                        const int* __restrict__ cu_q, const int* __restrict__ ctx_lens,
-                       __nv_bfloat16* __restrict__ out, int Hq, int Hkv, int max_blocks, float scale_log2) {
+                       __nv_bfloat16* __restrict__ out, int Hq, int Hkv, int max_blocks, int n_mtiles,
+                       float scale_log2) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                                ~static_cast<uintptr_t>(1023));
@@ -80,20 +110,26 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
     uint64_t* k_empty = bars + 5;
     uint64_t* v_full = bars + 9;
     uint64_t* v_empty = bars + 13;
-    uint64_t* s_full = bars + 17;       // [tile][buffer]: 4
-    uint64_t* p_full = bars + 21;       // [tile]: 2
-    uint64_t* o_done = bars + 23;       // [tile]: 2
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 25);
+    uint64_t* s_full = bars + 17;       // [tile][half]: 4
+    uint64_t* p_full = bars + 21;       // [tile][half]: 4
+    uint64_t* o_done = bars + 25;       // [tile][half]: 4
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 29);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int s = blockIdx.z, h = blockIdx.y;
+    // 1-D grid, fastest to slowest: the G query heads of one KV head | query tile pair, LAST first | KV head | sequence.
+    // Causal: later query tiles see more keys, so each (sequence, KV head) is worked heaviest tile first and the tail of
+    // the launch is made of short CTAs; the CTAs resident at one time share one or two KV heads' keys (L2 hits).
+    const int G = Hq / Hkv;
+    const int bx = blockIdx.x;
+    const int kvs = bx / (G * n_mtiles);
+    const int s = kvs / Hkv, h = (kvs % Hkv) * G + bx % G;
     const int q_begin = cu_q[s];
     const int n_q = cu_q[s + 1] - q_begin;
-    const int m0 = blockIdx.x * 2 * kTcBM;
+    const int m0 = (n_mtiles - 1 - (bx / G) % n_mtiles) * 2 * kTcBM;
     if (m0 >= n_q) return;  // whole CTA: before any barrier / TMEM use
     const int ctx = ctx_lens[s];
     const int off = ctx - n_q;  // query j sees keys [0, off + j]
-    const int g = h / (Hq / Hkv);
+    const int g = h / G;
     const bool has_b = m0 + kTcBM < n_q;                      // the second tile has at least one real row
     // keys each tile needs, in 64-key tiles (B's rows see up to 128 more keys than A's)
     const int nt_a = (min(ctx, off + m0 + kTcBM) + kTcBN - 1) / kTcBN;
@@ -112,8 +148,6 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
             mbar_init(&v_full[i], 1);
             mbar_init(&v_empty[i], 1);
             mbar_init(&s_full[i], 1);
-        }
-        for (int i = 0; i < 2; ++i) {
             mbar_init(&p_full[i], 128);
             mbar_init(&o_done[i], 1);
         }
@@ -124,11 +158,12 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
-    // columns: S_A[0] 0, S_A[1] 64, S_B[0] 128, S_B[1] 192, O_A 256, O_B 384
+    // columns: S_A 0, S_B 128, each as two 64-key halves of 64 columns (P of a half = bf16 pairs in the first 32
+    // columns of that half), O_A 256, O_B 384
     pdl_launch_dependents();
 
     if (warp == 0) {
-        // ===== TMA producer: the whole warp works. Lane p < 4 owns page p of a tile: the block-table lookups of
+        // ===== TMA producer: the whole warp works. Lane p < 8 owns page p of a tile: the block-table lookups of
         // a tile are one coalesced load, two tiles ahead of their use, and lane p issues its page's boxes.
         pdl_wait();  // q and this chunk's K/V rows come from the upstream kernels
         if (lane == 0) {
@@ -171,49 +206,67 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
         }
     } else if (warp == 1) {
         if (elect_one()) {
-            // ===== MMA issuer. tcgen05.mma execute in issue order, which is what makes the S buffers safe:
-            // QK_X(j+1) overwrites S_X[(j+1)&1], last read by softmax_X(j-1), whose P the issuer has waited for.
-            constexpr uint32_t idesc_qk = umma_idesc_bf16(kTcBM, kTcBN);                 // A, B K-major
+            // ===== MMA issuer. Four independent chains in rotation, (tile A | B) x (keys 0-63 | 64-127 of the 128-key
+            // K/V tile): for chain c and tile j   [wait P_c(j)]  P.V_c(j)  QK_c(j+1)  -> S_c(j+1)
+            // QK_c(j+1) overwrites exactly the columns P_c(j) sits in; tcgen05.mma execute in issue order, so that is
+            // safe once P.V_c(j) has been issued. While the softmax warps of a tile work on one half, the tensor pipe
+            // runs the three other chains: neither side waits for a whole tile of the other.
+            constexpr uint32_t idesc_qk = umma_idesc_bf16(kTcBM, kTcHalf);               // A, B K-major
             constexpr uint32_t idesc_pv = umma_idesc_bf16(kTcBM, kTcD) | (1u << 16);      // B (= V) MN-major
-            auto issue_qk = [&](int j) {
-                const int st = j % kKS;
-                mbar_wait(&k_full[st], (j / kKS) & 1);
-                tc_fence_after();
-                const uint32_t ka = smem_u32(sK + st * kKVTile);
+            auto issue_qk = [&](int t, int hf, int j) {
+                const uint32_t ka = smem_u32(sK + (j % kKS) * kKVTile) + hf * kTcHalf * 128;
+                const uint32_t qa = smem_u32(sQ + t * kQTile);
 #pragma unroll
-                for (int t = 0; t < 2; ++t) {
-                    if (t == 0 ? j >= nt_a : j >= nt_b) continue;
-                    const uint32_t qa = smem_u32(sQ + t * kQTile);
-                    const uint32_t d_tmem = tmem_base + t * 128 + (j & 1) * kTcBN;
-#pragma unroll
-                    for (int kk = 0; kk < kTcD / 16; ++kk)
-                        umma_bf16(d_tmem, umma_desc_sw128(qa + (kk >> 2) * kQAtom + (kk & 3) * 32),
-                                  umma_desc_sw128(ka + (kk >> 2) * kKVAtom + (kk & 3) * 32), idesc_qk, kk > 0 ? 1u : 0u);
-                    umma_commit(&s_full[t * 2 + (j & 1)]);
-                }
-                umma_commit(&k_empty[st]);
+                for (int kk = 0; kk < kTcD / 16; ++kk)
+                    umma_bf16(tmem_base + t * 128 + hf * kTcHalf,
+                              umma_desc_sw128(qa + (kk >> 2) * kQAtom + (kk & 3) * 32),
+                              umma_desc_sw128(ka + (kk >> 2) * kKVAtom + (kk & 3) * 32), idesc_qk, kk > 0 ? 1u : 0u);
+                umma_commit(&s_full[t * 2 + hf]);
             };
             mbar_wait(q_full, 0);
-            issue_qk(0);
+            mbar_wait(&k_full[0], 0);
+            tc_fence_after();
+#pragma unroll
+            for (int hf = 0; hf < 2; ++hf) {
+                if (0 < nt_a) issue_qk(0, hf, 0);
+                if (0 < nt_b) issue_qk(1, hf, 0);
+            }
+            umma_commit(&k_empty[0]);
             for (int j = 0; j < n_tiles; ++j) {
-                if (j + 1 < n_tiles) issue_qk(j + 1);  // overlaps the softmax of tile j
-                const int st = j % kVS;
-                mbar_wait(&v_full[st], (j / kVS) & 1);
-                const uint32_t va = smem_u32(sV + st * kKVTile);
+                const int vst = j % kVS;
+                bool v_ready = false, k_ready = false;
 #pragma unroll
-                for (int t = 0; t < 2; ++t) {
-                    if (t == 0 ? j >= nt_a : j >= nt_b) continue;
-                    mbar_wait(&p_full[t], j & 1);          // P_t(j) in smem, O_t rescaled, tail rows of V cleared
-                    tc_fence_after();
-                    const uint32_t pa = tmem_base + t * 128 + (j & 1) * kTcBN;   // P_t(j) lives where S_t(j) was
+                for (int hf = 0; hf < 2; ++hf) {
 #pragma unroll
-                    for (int kk = 0; kk < kTcBN / 16; ++kk)
-                        umma_bf16_ts(tmem_base + 256 + t * 128, pa + kk * 8,
-                                     umma_desc_sw128_mn(va + kk * 16 * 128, kKVAtom), idesc_pv,
-                                     (j > 0 || kk > 0) ? 1u : 0u);
-                    umma_commit(&o_done[t]);
+                    for (int t = 0; t < 2; ++t) {
+                        const int nt = t == 0 ? nt_a : nt_b;
+                        if (j < nt) {
+                            if (!v_ready) {
+                                mbar_wait(&v_full[vst], (j / kVS) & 1);
+                                v_ready = true;
+                            }
+                            mbar_wait(&p_full[t * 2 + hf], j & 1);   // P in TMEM, O rescaled, tail rows of V cleared
+                            tc_fence_after();
+                            const uint32_t va = smem_u32(sV + vst * kKVTile) + hf * kTcHalf * 128;
+#pragma unroll
+                            for (int kk = 0; kk < kTcHalf / 16; ++kk)
+                                umma_bf16_ts(tmem_base + 256 + t * 128, tmem_base + t * 128 + hf * kTcHalf + kk * 8,
+                                             umma_desc_sw128_mn(va + kk * 16 * 128, kKVAtom), idesc_pv,
+                                             (j > 0 || hf > 0 || kk > 0) ? 1u : 0u);
+                            umma_commit(&o_done[t * 2 + hf]);
+                        }
+                        if (j + 1 < nt) {
+                            if (!k_ready) {
+                                mbar_wait(&k_full[(j + 1) % kKS], ((j + 1) / kKS) & 1);
+                                tc_fence_after();
+                                k_ready = true;
+                            }
+                            issue_qk(t, hf, j + 1);
+                        }
+                    }
                 }
-                umma_commit(&v_empty[st]);
+                umma_commit(&v_empty[vst]);
+                if (j + 1 < n_tiles) umma_commit(&k_empty[(j + 1) % kKS]);
             }
         }
     } else {
@@ -230,15 +283,17 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
         const uint32_t tmem_S = tmem_base + t * 128 + lane_sel;
         const uint32_t tmem_O = tmem_base + 256 + t * 128 + lane_sel;
         float m_run = -INFINITY, l_run = 0.f;
-        for (int j = 0; j < nt; ++j) {
-            const int kv0 = j * kTcBN;
-            mbar_wait(&s_full[t * 2 + (j & 1)], (j >> 1) & 1);
+        for (int jj = 0; jj < 2 * nt; ++jj) {
+            const int j = jj >> 1, hf = jj & 1;          // K/V tile, half of it
+            const int kv0 = j * kTcBN + hf * kTcHalf;
+            const int c_idx = t * 2 + hf;                // this hand-over chain
+            mbar_wait(&s_full[c_idx], j & 1);
             tc_fence_after();
             uint32_t sv[4][16];                          // 64 scores: one TMEM round trip
 #pragma unroll
-            for (int c = 0; c < 4; ++c) tmem_ld16(tmem_S + (j & 1) * kTcBN + c * 16, sv[c]);
+            for (int c = 0; c < 4; ++c) tmem_ld16(tmem_S + hf * kTcHalf + c * 16, sv[c]);
             tmem_ld_wait();
-            if (kv0 + kTcBN - 1 > first_limit) {         // tile touches the causal boundary
+            if (kv0 + kTcHalf - 1 > first_limit) {       // touches the causal boundary
 #pragma unroll
                 for (int c = 0; c < 4; ++c)
 #pragma unroll
@@ -255,47 +310,51 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
             // maximum grow by more than 2^8 relative to it (P stays <= 256, exact in fp32 and fine in bf16; l
             // accumulates against the same reference, so the final O / l is unchanged). Rescaling O in TMEM is a
             // full round trip on the critical path and was taken on 97 % of tiles with an eager update.
-            const float cand = mx * scale_log2;  // -inf when the row has seen nothing in this tile
+            const float cand = mx * scale_log2;  // -inf when the row has seen nothing here
             float corr = 1.f;
             const bool moved = __any_sync(0xffffffffu, cand > m_run + 8.f);
             if (moved) {
                 const float mnew = fmaxf(m_run, cand);
-                corr = ex2_approx(m_run - mnew);   // first tile: 2^-inf = 0
+                corr = ex2_approx(m_run - mnew);   // first time: 2^-inf = 0
                 m_run = mnew;
             }
             const float mref = m_run == -INFINITY ? 0.f : m_run;
-            float ls4[4] = {0.f, 0.f, 0.f, 0.f};
+            const f32x2 sc2 = pack2(scale_log2, scale_log2), nm2 = pack2(-mref, -mref);
+            f32x2 ls2[2] = {pack2(0.f, 0.f), pack2(0.f, 0.f)};       // four independent sums
 #pragma unroll
             for (int c = 0; c < 4; ++c)
 #pragma unroll
                 for (int i = 0; i < 16; i += 2) {
-                    const float p0 = ex2_approx(fmaf(__uint_as_float(sv[c][i]), scale_log2, -mref));
-                    const float p1 = ex2_approx(fmaf(__uint_as_float(sv[c][i + 1]), scale_log2, -mref));
-                    ls4[(i >> 1) & 3] += p0 + p1;
+                    float x0, x1;
+                    unpack2(fma2(pack2(__uint_as_float(sv[c][i]), __uint_as_float(sv[c][i + 1])), sc2, nm2), x0, x1);
+                    const float p0 = ex2_approx(x0), p1 = ex2_approx(x1);
+                    ls2[(i >> 1) & 1] = add2(ls2[(i >> 1) & 1], pack2(p0, p1));
                     sv[c][i >> 1] = pack_bf16(p0, p1);
                 }
-            l_run = l_run * corr + (ls4[0] + ls4[1]) + (ls4[2] + ls4[3]);
-            // Stay at most one tile ahead of the tensor core: p_full is a one-bit-phase barrier, and a second
-            // arrival round before the issuer has seen the first would leave it waiting for ever. (P.V(j-1) has
-            // retired: also what the O rescale below needs.)
-            if (j > 0) mbar_wait(&o_done[t], (j - 1) & 1);
-            tc_fence_after();
-            // P as bf16 pairs into the first 32 columns of the S buffer just read (the A operand of P.V comes
-            // from TMEM: nothing of P crosses shared memory)
+            float la, lb, lc, ld;
+            unpack2(ls2[0], la, lb);
+            unpack2(ls2[1], lc, ld);
+            l_run = l_run * corr + (la + lb) + (lc + ld);
+            // P as bf16 pairs into the first 32 columns of the half just read (the A operand of P.V comes from
+            // TMEM: nothing of P crosses shared memory). No wait is needed here: QK of this chain was issued after
+            // its previous P.V, so that one has retired.
             {
                 uint32_t pw[16];
 #pragma unroll
-                for (int hlf = 0; hlf < 2; ++hlf) {
+                for (int qd = 0; qd < 2; ++qd) {
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
-                        pw[i] = sv[2 * hlf][i];
-                        pw[8 + i] = sv[2 * hlf + 1][i];
+                        pw[i] = sv[2 * qd][i];
+                        pw[8 + i] = sv[2 * qd + 1][i];
                     }
-                    tmem_st16(tmem_S + (j & 1) * kTcBN + hlf * 16, pw);
+                    tmem_st16(tmem_S + hf * kTcHalf + qd * 16, pw);
                 }
             }
-            // rescale this row of O only if some row of the warp moved its maximum
-            if (j > 0 && moved) {
+            // rescale this row of O only if some row of the warp moved its maximum; the P.V of the OTHER half
+            // (issued one hand-over ago) may still be accumulating into O: wait for it first
+            if (jj > 0 && moved) {
+                mbar_wait(&o_done[t * 2 + (hf ^ 1)], (hf ? j : j - 1) & 1);
+                tc_fence_after();
 #pragma unroll 1
                 for (int c = 0; c < kTcD; c += 16) {
                     uint32_t v[16];
@@ -309,10 +368,10 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
             tmem_st_wait();
             // keys past the context in the last tile: their V rows are stale page contents or never-loaded
             // shared memory; P is 0 there but 0 * NaN would poison O, so clear those rows (both dim-atoms)
-            if (kv0 + kTcBN > ctx) {
+            if (kv0 + kTcHalf > ctx) {
                 mbar_wait(&v_full[j % kVS], (j / kVS) & 1);
-                const int valid = ctx - kv0;
-                if (row < kTcBN && row >= valid) {
+                const int valid = ctx - j * kTcBN;       // rows of the 128-key tile that hold real keys
+                if ((row >> 6) == hf && row >= valid) {
                     uint8_t* vrow = sV + (j % kVS) * kKVTile + row * 128;
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
@@ -323,11 +382,11 @@ attn_prefill_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_con
                 fence_proxy_async();   // generic-proxy smem writes (cleared V rows) -> visible to the tensor core
             }
             tc_fence_before();
-            mbar_arrive(&p_full[t]);
+            mbar_arrive(&p_full[c_idx]);
         }
         // ---- epilogue: O / l -> bf16, one 256-byte row per thread
         if (nt > 0) {
-            mbar_wait(&o_done[t], (nt - 1) & 1);
+            mbar_wait(&o_done[t * 2 + 1], (nt - 1) & 1);   // the last P.V of this tile
             tc_fence_after();
             const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
             __nv_bfloat16* orow = out + (static_cast<long long>(q_begin + qpos) * Hq + h) * kTcD;
@@ -428,13 +487,18 @@ int launch_prefill_tc(const void* q, const void* kc, const void* vc, const int* 
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = (flags & ATX_FLAG_PDL) ? 1 : 0;
-    cfg.gridDim = dim3(static_cast<unsigned>((max_q_len + 2 * kTcBM - 1) / (2 * kTcBM)), static_cast<unsigned>(Hq),
-                       static_cast<unsigned>(S));
+    const int n_mtiles = (max_q_len + 2 * kTcBM - 1) / (2 * kTcBM);
+    const long long n_ctas = static_cast<long long>(n_mtiles) * Hq * S;
+    if (n_ctas > 0x7fffffffll) {
+        set_error("atx_paged_attn_prefill: %lld CTAs exceed the grid limit", n_ctas);
+        return ATX_ERR_LIMIT;
+    }
+    cfg.gridDim = dim3(static_cast<unsigned>(n_ctas));
     cfg.blockDim = dim3(kTcThreads);
     cfg.dynamicSmemBytes = kTcSmem;
     cfg.stream = stream;
     ATX_CUDA(cudaLaunchKernelEx(&cfg, attn_prefill_tc_kernel, tmQ, tmK, tmV, bt, cu_q, ctx,
-                                reinterpret_cast<__nv_bfloat16*>(out), Hq, Hkv, max_blocks,
+                                reinterpret_cast<__nv_bfloat16*>(out), Hq, Hkv, max_blocks, n_mtiles,
                                 scale * 1.4426950408889634f));
     return ATX_OK;
 }

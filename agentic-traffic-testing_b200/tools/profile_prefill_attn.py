@@ -23,3 +23,13 @@ ctx = torch.full((S,), L, device="cuda", dtype=torch.int32)
 for _ in range(3):
     _cabi.paged_attn_prefill(q, kc, vc, bt, cu, ctx, out, S, L, Hq, Hkv, D, bs, D ** -0.5)
 torch.cuda.synchronize()
+if len(sys.argv) > 1:      # any argument: CUDA-event timing instead of a run for ncu
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(10):
+        _cabi.paged_attn_prefill(q, kc, vc, bt, cu, ctx, out, S, L, Hq, Hkv, D, bs, D ** -0.5)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 10
+    flops = 4 * D * Hq * S * L * (L + 1) / 2
+    print(f"S={S} x {L}: {ms:.3f} ms = {flops / ms / 1e9:.0f} TFLOP/s causal")
