@@ -57,9 +57,9 @@ class ModelRunner:
         self.Tmax = max(16, e.max_num_batched_tokens)
         self.Smax = max(1, e.max_num_seqs)
         self.bs = e.block_size
-        if self.bs <= 0 or self.bs % 16:
-            raise ValueError(f"block_size={self.bs}: KV pages hold a multiple of 16 tokens (vLLM's default 16; "
-                             "the attention kernels stage whole 16-token tiles)")
+        if self.bs != 16:
+            raise ValueError(f"block_size={self.bs}: KV pages hold 16 tokens (vLLM's default; the prefill attention "
+                             "loads one page of one KV head per TMA box)")
         self.MB = (e.max_model_len + self.bs - 1) // self.bs
         self.tp, self.tp_rank, self.tp_group = max(1, e.tp_size), e.tp_rank, None
         tp = self.tp

@@ -186,7 +186,8 @@ int atx_paged_attn_decode_static(const void* q, const void* k_cache, const void*
  * rows [cu_q[s], cu_q[s+1]) of q, and their keys are the first ctx_lens[s] cache tokens of that
  * sequence (the chunk's own K/V must already be in the cache): query j of n attends to keys
  * [0, ctx_lens[s] - n + j]. q/out: [total_q, Hq * D] bf16 (total_q = cu_q[S]); num_blocks = blocks in
- * each cache (both only bound the TMA descriptors of the tcgen05 path: head_dim 128, 16-token pages). */
+ * each cache (they bound the TMA descriptors). One kernel, on tcgen05: head_dim 64 | 128, block_size 16,
+ * 16-byte aligned buffers; anything else returns ATX_ERR_UNSUPPORTED. */
 int atx_paged_attn_prefill(const void* q, const void* k_cache, const void* v_cache, const int* block_table,
                            const int* cu_q, const int* ctx_lens, void* out, int S, int max_q_len,
                            long long total_q, long long num_blocks, int Hq, int Hkv, int D, int block_size,

@@ -658,3 +658,18 @@ def test_decode_attention_refuses_unsupported_shapes(cabi):
         cabi.paged_attn_decode(q, kc.cuda(), vc.cuda(), bt.cuda(), sl, out, None, 1, 8, 2, 64, 8, 1, 0.125)
     with pytest.raises(cabi.AtxError, match="at most 8 query heads"):
         cabi.paged_attn_decode(q, kc.cuda(), vc.cuda(), bt.cuda(), sl, out, None, 1, 32, 2, 64, 16, 1, 0.125)
+
+
+def test_prefill_attention_refuses_unsupported_shapes(cabi):
+    """One prefill attention kernel (tcgen05, head_dim 64 | 128, 16-token pages): other shapes are refused, not
+    routed to a slower path."""
+    kc, vc, bt, ks, vs = _paged_case(4, [40], 8, 2, 64)
+    q = _bf16(torch.randn(40, 8 * 64)).cuda()
+    out = torch.empty_like(q)
+    cu = torch.tensor([0, 40], dtype=torch.int32).cuda()
+    ctx = torch.tensor([40], dtype=torch.int32).cuda()
+    with pytest.raises(cabi.AtxError, match="unsupported head_dim"):
+        cabi.paged_attn_prefill(q, kc.cuda(), vc.cuda(), bt.cuda(), cu, ctx, out, 1, 40, 8, 2, 64, 32, 0.125)
+    with pytest.raises(cabi.AtxError, match="unsupported head_dim"):
+        cabi.paged_attn_prefill(q, kc.cuda(), vc.cuda(), bt.cuda(), cu, ctx, out, 1, 40, 16, 4, 32, 16, 0.125)
+

@@ -167,7 +167,7 @@ def _segment_values(L, Hkv, D, g, seg=1024):
 
 
 def test_prefill_lazy_rescale_branch_taken_and_not_taken(cabi):
-    """attn_prefill_tc.cu rescales O in TMEM only when a row's running maximum grew by more than 2^8 since the
+    """attn_prefill.cu rescales O in TMEM only when a row's running maximum grew by more than 2^8 since the
     reference was last moved. Three score profiles over 16 384 keys drive that branch both ways, hundreds of
     tiles into the sequence:
       rising steps  - the maximum jumps by ~2^13 every 1 536 keys (rescale taken late and often; everything
