@@ -5,6 +5,10 @@ the engine arguments the reference passes (`max_model_len`, `max_num_seqs=12`, `
 `gpu_memory_utilization=0.90`, `dtype=bfloat16`, prefix caching on as in vLLM V1's default).
 
     python agentic-traffic-testing_b200/tools/vllm_comparator.py --steps 5 --warmup 3
+    python agentic-traffic-testing_b200/tools/vllm_comparator.py --model 70b --tp 8 --batch 32 --steps 2 --warmup 1
+
+The second form is BASELINE configs[3] (Llama-3.1-70B shape, tensor parallel over the 8 GPUs of the box, fan-out batch
+32) with the bursts `bench.py`'s tp70b record uses: vLLM's own fused all-reduce + RMSNorm path next to ours.
 
 Prints one JSON line; exits 0 with {"unavailable": ...} if vLLM cannot be brought up offline. Wall-clock timed
 (vLLM owns its streams); the number is reported beside bench.py's, never as bench.py's value.
@@ -33,11 +37,17 @@ LLAMA_8B = {
 }
 
 
+LLAMA_70B = dict(LLAMA_8B, hidden_size=8192, intermediate_size=28672, num_hidden_layers=80, num_attention_heads=64)
+
+
 def main() -> int:
     ap = argparse.ArgumentParser()
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--eager", action="store_true", help="no torch.compile / CUDA graphs in vLLM")
+    ap.add_argument("--model", default="8b", choices=["8b", "70b"])
+    ap.add_argument("--tp", type=int, default=1)
+    ap.add_argument("--batch", type=int, default=0, help="default: bench.py's burst of 6")
     a = ap.parse_args()
     os.environ.setdefault("HF_HUB_OFFLINE", "1")
     os.environ.setdefault("TRANSFORMERS_OFFLINE", "1")
@@ -47,18 +57,30 @@ def main() -> int:
     os.environ.setdefault("VLLM_HOST_IP", "127.0.0.1")
     from bench import BATCH, OUT, PROMPT, SHARED, burst_prompts  # the same bursts bench.py times
 
+    if a.batch:         # the tp70b record's bursts (bench.py:tp70b_measure): rng seed 4 + step, shared 768 + 256 own
+        import numpy as np
+
+        BATCH = a.batch
+
+        def burst_prompts(step):  # noqa: F811
+            rng = np.random.default_rng(4 + step)
+            shared = rng.integers(0, 128000, SHARED).tolist()
+            return [shared + rng.integers(0, 128000, PROMPT - SHARED).tolist() for _ in range(BATCH)]
+    cfg = LLAMA_70B if a.model == "70b" else LLAMA_8B
+
     out = {"impl": "vllm-comparator", "metric": "decode tokens/s", "workload":
            f"fan-out burst batch {BATCH}, prompt {PROMPT} (shared prefix {SHARED}), {OUT} greedy tokens",
-           "weights": "dummy (load_format=dummy), Llama-3.1-8B shape, bf16"}
+           "weights": f"dummy (load_format=dummy), Llama-3.1-{a.model.upper()} shape, bf16", "tensor_parallel": a.tp}
     try:
         import vllm
         from vllm import LLM, SamplingParams
 
         out["vllm"] = vllm.__version__
         d = tempfile.mkdtemp(prefix="llama8b_cfg_")
-        (Path(d) / "config.json").write_text(json.dumps(LLAMA_8B))
+        (Path(d) / "config.json").write_text(json.dumps(cfg))
         llm = LLM(model=d, load_format="dummy", skip_tokenizer_init=True, dtype="bfloat16", max_model_len=4096,
-                  max_num_seqs=12, max_num_batched_tokens=8192, gpu_memory_utilization=0.90,
+                  max_num_seqs=max(12, BATCH), max_num_batched_tokens=8192, gpu_memory_utilization=0.90,
+                  tensor_parallel_size=a.tp,
                   enable_prefix_caching=True, enforce_eager=a.eager, seed=0, disable_log_stats=False)
         sp = SamplingParams(temperature=0.0, max_tokens=OUT, ignore_eos=True, detokenize=False)
         times, ttfts = [], []
