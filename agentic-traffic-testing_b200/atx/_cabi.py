@@ -25,8 +25,7 @@ FLAG_ORDERED = 2   # atx_gemm_run ADD_F32, T <= 64: fixed-order split-K (bit-rep
 EXPORTS = [
     "atx_last_error", "atx_version", "atx_device_info",
     "atx_gemm_plan_create", "atx_gemm_plan_destroy", "atx_gemm_run", "atx_gemm_auto_splits",
-    "atx_gemm_set_l2_prefetch",
-    "atx_embed_gather", "atx_rmsnorm", "atx_rope_kv_write", "atx_silu_mul", "atx_allreduce_add_rmsnorm",
+    "atx_embed_gather", "atx_rmsnorm", "atx_rope_kv_write", "atx_silu_mul",
     "atx_reduce_scatter_rmsnorm_all_gather", "atx_allreduce_add_rmsnorm_ll",
     "atx_paged_attn_decode_workspace_bytes", "atx_paged_attn_decode", "atx_paged_attn_prefill",
     "atx_paged_attn_decode_static", "atx_paged_attn_decode_static_capacity",
@@ -71,12 +70,8 @@ def load() -> C.CDLL:
     lib.atx_gemm_plan_destroy.restype = None
     lib.atx_gemm_run.argtypes = [vp, vp, i64, i32, i32, i32, i32, vp]
     lib.atx_gemm_auto_splits.argtypes = [i64, i64, i32]
-    lib.atx_gemm_set_l2_prefetch.argtypes = [i32]
-    lib.atx_gemm_set_l2_prefetch.restype = None
     lib.atx_embed_gather.argtypes = [vp, vp, vp, i32, i32, i32, vp]
     lib.atx_rmsnorm.argtypes = [vp, vp, vp, vp, vp, i32, i32, f32, vp, i64, i32, vp]
-    lib.atx_allreduce_add_rmsnorm.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), vp, i32, vp, i32, i32, vp, vp, vp, i32,
-                                              i32, f32, vp, i64, i32, vp]
     lib.atx_reduce_scatter_rmsnorm_all_gather.argtypes = [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), vp, i32, vp,
                                                           i32, i32, vp, vp, i32, i32, f32, vp, i64, i32, vp]
     lib.atx_allreduce_add_rmsnorm_ll.argtypes = [vp, vp, C.POINTER(vp), C.POINTER(vp), vp, i32, vp, i64, i32, i32, i32,

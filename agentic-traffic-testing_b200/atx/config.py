@@ -175,6 +175,8 @@ class EngineConfig:
     async_scheduling: bool = True   # launch decode step N+1 before the host has read step N's tokens
     deterministic: bool = False     # split-K sums in a fixed order (ATX_FLAG_ORDERED): same tokens bit for bit on
     #                                 every run of the same batches, a few percent slower per decode step
+    tp_allreduce: str = "auto"      # tensor parallel: "auto" = our fused all-reduce + add + norm kernels for steps of up
+    #                                 to 256 rows (push form up to 64), NCCL beyond; "nccl" = NCCL for every step
     device: int = 0
     tp_size: int = 1          # tensor-parallel ranks sharing one model (70B); needs torch.distributed NCCL
     tp_rank: int = 0

@@ -85,15 +85,12 @@ class ModelRunner:
         self.act = torch.zeros(T, I, dtype=bf, device=dev)
         self.part = torch.zeros(T, H, dtype=f32, device=dev) if tp > 1 else None  # partial o/down sums (TP)
         self.allreduce_calls = 0
-        self.fused_ar = False      # all-reduce + add + norm in our own kernel over peer memory
-        self.sharded_ar = False    # ... in its two-shot form (reduce-scatter by row, all-gather of the bf16 rows)
-        self.ll_ar = False         # ... in its low-latency push form for decode-sized steps (data is the flag)
+        self.fused_ar = False      # all-reduce + add + norm in our own kernels over peer memory (else: NCCL + norm kernel)
         self.xn = self.xn2 = self.xl = None
-        ar_mode = os.environ.get("ATX_TP_ALLREDUCE", "ll")
-        if ar_mode not in ("fused", "sharded", "ll", "nccl"):
-            raise ValueError(f"ATX_TP_ALLREDUCE={ar_mode!r}: expected ll | fused | sharded | nccl")
-        if tp > 1 and ar_mode != "nccl":
-            self._setup_fused_allreduce(T, H, ar_mode, S)
+        if e.tp_allreduce not in ("auto", "nccl"):
+            raise ValueError(f"tp_allreduce={e.tp_allreduce!r}: expected auto | nccl")
+        if tp > 1 and e.tp_allreduce != "nccl":
+            self._setup_fused_allreduce(T, H, S)
         if self.xn is None:   # (the two-shot kernels need them in peer-mapped memory: allocated above)
             self.xn = torch.zeros(T, H, dtype=bf, device=dev)
             self.xl = torch.zeros(S, H, dtype=bf, device=dev)
@@ -175,8 +172,6 @@ class ModelRunner:
         self.stream = torch.cuda.Stream(device=dev)   # every launch and copy of this runner
         self._h2d_done = torch.cuda.Event()
         self.flags = (_cabi.FLAG_PDL if e.use_pdl else 0) | (_cabi.FLAG_ORDERED if e.deterministic else 0)
-        self.lib.atx_gemm_set_l2_prefetch(int(os.environ.get("ATX_L2_PREFETCH_KB", "0")))
-        self.tp_l2_prefetch_kb = int(os.environ.get("ATX_TP_L2_PREFETCH_KB", "0"))
         self.scale = float(m.head_dim) ** -0.5
         self.launches_last_step = 0
         self.kernel_launches = 0  # cumulative count of our kernels launched (graph replays included)
@@ -215,15 +210,12 @@ class ModelRunner:
         dp = self._dp
         h, xn, qkv, q, attn, act = (t.data_ptr() for t in (self.h, self.xn, self.qkv, self.q, self.attn, self.act))
         fused = tp > 1 and self.fused_ar and T <= self.FUSED_AR_MAX_T
-        self._ll_now = fused and self.ll_ar and T <= self.LL_AR_MAX_T
+        self._ll_now = fused and T <= self.LL_AR_MAX_T
         xn2 = self.xn2.data_ptr()
         if self._ll_now:
             # steps that took another path may have left plain data in the first activation buffer: re-arm it
             # (the other one and xl are re-armed by the first all-reduce call below)
             self._arm_a.fill_(-32768)
-        # GEMMs that follow a fused all-reduce sit idle behind a cross-GPU barrier while HBM is idle too: let
-        # them pull their weight slices into L2 before they wait (per-call ATX_FLAG_L2_PREFETCH)
-        fl_ar = fl | ((self.tp_l2_prefetch_kb & 0xFF) << 8) if (fused and fl) else fl
         if tp == 1:
             targets = (h, h)                      # projections add straight into the residual stream
         elif fused:
@@ -267,10 +259,10 @@ class ModelRunner:
             kc, vc = self.k_cache[li].data_ptr(), self.v_cache[li].data_ptr()
             if sp_qkv > 1:   # split-K accumulates into qkv: the norm kernel's spare CTAs clear it
                 norm(l.ln1.data_ptr(), xn, qkv, T * qkv_size * 4)
-                ck(lib.atx_gemm_run(p_qkv._h, qkv, qkv_size, T, _cabi.GEMM_ADD_F32, sp_qkv, fl_ar, st))
+                ck(lib.atx_gemm_run(p_qkv._h, qkv, qkv_size, T, _cabi.GEMM_ADD_F32, sp_qkv, fl, st))
             else:
                 norm(l.ln1.data_ptr(), xn)
-                ck(lib.atx_gemm_run(p_qkv._h, qkv, qkv_size, T, _cabi.GEMM_STORE_F32, 1, fl_ar, st))
+                ck(lib.atx_gemm_run(p_qkv._h, qkv, qkv_size, T, _cabi.GEMM_STORE_F32, 1, fl, st))
             n += 1
             ck(lib.atx_rope_kv_write(qkv, dp["pos"], dp["slots"], self.rope.data_ptr(), q, kc, vc, T, Hq, Hkv, D,
                                      self.bs, fl, st))
@@ -287,7 +279,7 @@ class ModelRunner:
                 n += 1
             project(p_o)
             norm(l.ln2.data_ptr(), xn2)
-            ck(lib.atx_gemm_run(p_gu._h, act, I, T, _cabi.GEMM_SWIGLU_BF16, 0, fl_ar, st))  # silu(g)*u in the epilogue
+            ck(lib.atx_gemm_run(p_gu._h, act, I, T, _cabi.GEMM_SWIGLU_BF16, 0, fl, st))  # silu(g)*u in the epilogue
             n += 1
             project(p_down)
         if n_rows:
@@ -328,12 +320,11 @@ class ModelRunner:
     # co-resident (rows x H/2048 CTAs <= 2 x SMs)
     LL_AR_MAX_T = 64
 
-    def _setup_fused_allreduce(self, T: int, H: int, mode: str = "fused", S: int = 0) -> None:
-        """Symmetric (peer-mapped) ping-pong partial buffers + flag arrays for atx_allreduce_add_rmsnorm.
-        torch's symmetric-memory allocator is used only to obtain peer-mapped memory; the kernel is ours.
-        Modes 'sharded' and 'll' (the two-shot kernels): the activation buffers xn2 / xl / xn then live in one more
-        symmetric allocation, because every rank writes its rows into every rank's copy; 'll' adds the receive
-        slots of the push protocol and arms everything with the sentinel."""
+    def _setup_fused_allreduce(self, T: int, H: int, S: int) -> None:
+        """Symmetric (peer-mapped) memory for the two all-reduce + add + norm kernels: ping-pong partial buffers and
+        flag arrays (flag-barrier form), the activation buffers xn2 / xl / xn (every rank writes its rows into every
+        rank's copy), and the receive slots of the push form, armed with the sentinel. torch's symmetric-memory
+        allocator is used only to obtain peer-mapped memory; the kernels are ours."""
         import torch.distributed as dist
         import torch.distributed._symmetric_memory as symm
 
@@ -346,19 +337,15 @@ class ModelRunner:
             self.sym_flags = symm.empty((64,), dtype=torch.int32, device=self.dev)
             self.sym_flags.zero_()
             hf = symm.rendezvous(self.sym_flags, group)
-            hx = hr = None
-            if mode in ("sharded", "ll"):
-                # activation buffers every rank writes into: A = xn2 [T, H] (gate_up input), xl [S, H] (LM-head
-                # input), B = xn [T, H] (qkv input); xl and the head of B are contiguous (one re-arm region)
-                self.sym_x = symm.empty((2 * T + S, H), dtype=torch.bfloat16, device=self.dev)
-                self.sym_x.zero_()
-                hx = symm.rendezvous(self.sym_x, group)
-            if mode == "ll":
-                cap = min(T, self.LL_AR_MAX_T)
-                self.sym_rs = symm.empty((2, self.tp, cap, H), dtype=torch.float32, device=self.dev)
-                self.sym_rs.fill_(-0.0)                                    # the sentinel: "nothing has arrived"
-                hr = symm.rendezvous(self.sym_rs, group)
-                self.sym_x.view(torch.int16).fill_(-32768)                 # bf16 -0.0
+            # activation buffers every rank writes into: A = xn2 [T, H] (gate_up input), xl [S, H] (LM-head
+            # input), B = xn [T, H] (qkv input); xl and the head of B are contiguous (one re-arm region)
+            self.sym_x = symm.empty((2 * T + S, H), dtype=torch.bfloat16, device=self.dev)
+            hx = symm.rendezvous(self.sym_x, group)
+            cap = min(T, self.LL_AR_MAX_T)
+            self.sym_rs = symm.empty((2, self.tp, cap, H), dtype=torch.float32, device=self.dev)
+            self.sym_rs.fill_(-0.0)                                    # the sentinel: "nothing has arrived"
+            hr = symm.rendezvous(self.sym_rs, group)
+            self.sym_x.view(torch.int16).fill_(-32768)                 # bf16 -0.0
         except Exception as exc:  # no peer mapping on this box: keep the NCCL path, loudly
             print(f"[atx] symmetric memory unavailable ({exc!r}); tensor-parallel all-reduce stays on NCCL", flush=True)
             return
@@ -368,19 +355,14 @@ class ModelRunner:
         self._ar_flags = (vp * self.tp)(*[int(p) for p in hf.buffer_ptrs])
         self._ar_state = torch.zeros(2, dtype=torch.int32, device=self.dev)
         self._ar_handles = (hp, hf, hx, hr)
-        if hx is not None:
-            self.xn2, self.xl, self.xn = self.sym_x[:T], self.sym_x[T:T + S], self.sym_x[T + S:]
-            self._ar_x_base = [int(p) for p in hx.buffer_ptrs]
-            self._ar_out_ptrs = {}     # byte offset into sym_x -> array of the peers' pointers
-            self.sharded_ar = True
-        if hr is not None:
-            cap = self.sym_rs.shape[2]
-            self._ll_cap = cap
-            self._ll_rs = [(vp * self.tp)(*[int(p) + b * self.tp * cap * H * 4 for p in hr.buffer_ptrs]) for b in (0, 1)]
-            # parity 0 writes A and re-arms xl + the head of B; parity 1 writes B (or xl) and re-arms the head of A
-            self._ll_reset = [(self.xl.data_ptr(), (S + cap) * H * 2), (self.xn2.data_ptr(), cap * H * 2)]
-            self._arm_a = self.sym_x[:cap].view(torch.int16)
-            self.ll_ar = True
+        self.xn2, self.xl, self.xn = self.sym_x[:T], self.sym_x[T:T + S], self.sym_x[T + S:]
+        self._ar_x_base = [int(p) for p in hx.buffer_ptrs]
+        self._ar_out_ptrs = {}     # byte offset into sym_x -> array of the peers' pointers
+        self._ll_cap = cap
+        self._ll_rs = [(vp * self.tp)(*[int(p) + b * self.tp * cap * H * 4 for p in hr.buffer_ptrs]) for b in (0, 1)]
+        # parity 0 writes A and re-arms xl + the head of B; parity 1 writes B (or xl) and re-arms the head of A
+        self._ll_reset = [(self.xl.data_ptr(), (S + cap) * H * 2), (self.xn2.data_ptr(), cap * H * 2)]
+        self._arm_a = self.sym_x[:cap].view(torch.int16)
         torch.cuda.synchronize(self.dev)
         dist.barrier(group=group)
         self.fused_ar = True
@@ -390,35 +372,24 @@ class ModelRunner:
         """all-reduce(part[buf]) + residual add + RMSNorm; hands the other buffer back zeroed."""
         m = self.m
         other = self.sym_part[1 - buf].data_ptr()
-        if self.sharded_ar:
-            off = out_ptr - self.sym_x.data_ptr()
-            if self._ll_now:
-                outs = self._ar_out_ptrs.get(off)
-                if outs is None:
-                    outs = self._ar_out_ptrs[off] = (C.c_void_p * self.tp)(*[b + off for b in self._ar_x_base])
-                in_a = off < self.xl.data_ptr() - self.sym_x.data_ptr()
-                assert in_a == (buf == 0), "activation buffer does not match the all-reduce parity"
-                reset_ptr, reset_bytes = self._ll_reset[buf]
-                self._ck(self.lib.atx_allreduce_add_rmsnorm_ll(
-                    self.h.data_ptr(), self.sym_part[buf].data_ptr(), self._ll_rs[buf], outs, other, T, reset_ptr,
-                    reset_bytes, self._ll_cap, self.tp_rank, self.tp, rows_ptr, w_ptr, n_rows, m.hidden_size,
-                    m.rms_norm_eps, zero_ptr, zero_bytes, self.flags, st))
-                self.allreduce_calls += 1
-                return
-            outs = self._ar_out_ptrs.get(off)
-            if outs is None:
-                assert 0 <= off < self.sym_x.numel() * 2, "two-shot all-reduce output must live in the symmetric buffer"
-                outs = self._ar_out_ptrs[off] = (C.c_void_p * self.tp)(*[b + off for b in self._ar_x_base])
+        off = out_ptr - self.sym_x.data_ptr()
+        outs = self._ar_out_ptrs.get(off)
+        if outs is None:
+            assert 0 <= off < self.sym_x.numel() * 2, "all-reduce output must live in the symmetric buffer"
+            outs = self._ar_out_ptrs[off] = (C.c_void_p * self.tp)(*[b + off for b in self._ar_x_base])
+        if self._ll_now:      # decode-sized: the push form
+            in_a = off < self.xl.data_ptr() - self.sym_x.data_ptr()
+            assert in_a == (buf == 0), "activation buffer does not match the all-reduce parity"
+            reset_ptr, reset_bytes = self._ll_reset[buf]
+            self._ck(self.lib.atx_allreduce_add_rmsnorm_ll(
+                self.h.data_ptr(), self.sym_part[buf].data_ptr(), self._ll_rs[buf], outs, other, T, reset_ptr,
+                reset_bytes, self._ll_cap, self.tp_rank, self.tp, rows_ptr, w_ptr, n_rows, m.hidden_size,
+                m.rms_norm_eps, zero_ptr, zero_bytes, self.flags, st))
+        else:                 # up to FUSED_AR_MAX_T rows: the flag-barrier form
             self._ck(self.lib.atx_reduce_scatter_rmsnorm_all_gather(
                 self.h.data_ptr(), self._ar_parts[buf], self._ar_flags, outs, other, T, self._ar_state.data_ptr(),
                 self.tp_rank, self.tp, rows_ptr, w_ptr, n_rows, m.hidden_size, m.rms_norm_eps, zero_ptr, zero_bytes,
                 self.flags, st))
-            self.allreduce_calls += 1
-            return
-        self._ck(self.lib.atx_allreduce_add_rmsnorm(
-            self.h.data_ptr(), self._ar_parts[buf], self._ar_flags, other, T, self._ar_state.data_ptr(), self.tp_rank,
-            self.tp, rows_ptr, w_ptr, out_ptr, n_rows, m.hidden_size, m.rms_norm_eps, zero_ptr, zero_bytes, self.flags,
-            st))
         self.allreduce_calls += 1
 
     def _all_reduce(self, t: torch.Tensor) -> None:
@@ -485,9 +456,8 @@ class ModelRunner:
         if T_real > self.Tmax or n_dec + n_pf > self.Smax:
             raise RuntimeError("step exceeds the runner's static capacity")
         # TP steps contain NCCL all-reduces: they capture fine (thread-local capture mode), but the graphs
-        # must be dropped before the process group is destroyed (close()). ATX_TP_GRAPHS=0 opts out.
-        use_graph = self.e.enable_cuda_graphs and (self.tp == 1 or os.environ.get("ATX_TP_GRAPHS", "1") != "0") \
-            and n_pf == 0 and _bucket(n_dec, _GRAPH_BUCKETS) is not None \
+        # must be dropped before the process group is destroyed (close()).
+        use_graph = self.e.enable_cuda_graphs and n_pf == 0 and _bucket(n_dec, _GRAPH_BUCKETS) is not None \
             and _bucket(n_dec, _GRAPH_BUCKETS) <= self.Smax
         B = _bucket(n_dec, _GRAPH_BUCKETS) if use_graph else n_dec
         T = B + (T_real - n_dec)

@@ -127,14 +127,6 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* m
           "r"(c1), "l"(policy)
         : "memory");
 }
-// Pull one box of a tiled tensor into L2 only (no shared memory, no barrier): keeps HBM streaming
-// while the CTA is still waiting for its other operand.
-__device__ __forceinline__ void tma_prefetch_l2_2d(const CUtensorMap* m, int c0, int c1) {
-    asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global [%0, {%1, %2}];" ::"l"(
-                     reinterpret_cast<uint64_t>(m)),
-                 "r"(c0), "r"(c1)
-                 : "memory");
-}
 // 1-D bulk copy global -> shared, completion on an mbarrier (bytes multiple of 16, 16-B aligned).
 __device__ __forceinline__ void bulk_load_1d(void* smem_dst, const void* gsrc, uint32_t bytes,
                                              uint64_t* bar) {

@@ -63,7 +63,7 @@ template <int TN>
 __global__ void __launch_bounds__(kGemmThreads)
 gemm_wt_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmX,
                void* __restrict__ out, long long ldo, int T, int N, int kb_total, int kb_per_split,
-               int mode_in, int w_evict_first, int l2_prefetch_kb, int stages) {
+               int mode_in, int w_evict_first, int stages) {
     const int mode = mode_in & 0xff;
     const bool ordered = (mode_in & 0x100) != 0;   // ATX_FLAG_ORDERED: split-K summed in a fixed order (below)
     // `stages` (<= Cfg::kStages) is the ring depth actually used: CTAs with few k-blocks get a smaller
@@ -120,9 +120,6 @@ gemm_wt_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ 
                     tma_load_2d(smem + i * Cfg::kStageBytes, &tmW, &full_bar[i],
                                 (kb_begin + i) * kBK, n0, polW);
                 }
-                // ... and the next slices go to L2, so HBM keeps streaming through the dependency gap
-                const int ahead = min(nkb, pre + l2_prefetch_kb);
-                for (int i = pre; i < ahead; ++i) tma_prefetch_l2_2d(&tmW, (kb_begin + i) * kBK, n0);
                 pdl_wait();
                 for (int i = 0; i < pre; ++i) {
                     tma_load_2d(smem + i * Cfg::kStageBytes + Cfg::kStageBytesW, &tmX, &full_bar[i],
@@ -619,10 +616,6 @@ struct atx_gemm_plan {
 
 using namespace atx;
 
-// k-blocks (16 KB each) of weights a CTA prefetches into L2 before it waits for the upstream grid
-static thread_local int tl_l2_prefetch_kb = 0;
-static int g_l2_prefetch_kb = 0;  // measured on B200: prefetching ahead of the TMA ring costs bandwidth (r01)
-
 template <int TN>
 static int launch_gemm(const atx_gemm_plan* p, int ti, void* out, long long ldo, int T, int mode,
                        int splits, int pdl, cudaStream_t stream) {
@@ -673,8 +666,7 @@ static int launch_gemm(const atx_gemm_plan* p, int ti, void* out, long long ldo,
     cfg.attrs = attr;
     cfg.numAttrs = na;
     ATX_CUDA(cudaLaunchKernelEx(&cfg, gemm_wt_kernel<TN>, p->tmW, p->tmX[ti], out, ldo, T,
-                                static_cast<int>(p->N), kb_total, kb_per, mode, p->w_evict_first,
-                                pdl ? tl_l2_prefetch_kb : 0, stages));
+                                static_cast<int>(p->N), kb_total, kb_per, mode, p->w_evict_first, stages));
     return ATX_OK;
 }
 
@@ -738,8 +730,6 @@ int atx_gemm_plan_create(atx_gemm_plan** plan, const void* W, long long N, long 
 
 void atx_gemm_plan_destroy(atx_gemm_plan* plan) { delete plan; }
 
-void atx_gemm_set_l2_prefetch(int k_blocks) { g_l2_prefetch_kb = k_blocks < 0 ? 0 : k_blocks; }
-
 int atx_gemm_auto_splits(long long N, long long K, int T) {
     // Decode-sized batches are pure weight streaming. Two CTAs fit per SM (shared memory), so cut K
     // until the grid fills ONE wave of 2 x SMs CTAs (no tail wave), keeping >= 4 k-blocks per CTA.
@@ -788,8 +778,6 @@ int atx_gemm_run(const atx_gemm_plan* p, void* out, long long ldo, int T, int mo
                 "atx_gemm_run: SWIGLU split-K needs T <= 64 and splits in {2,4,8} dividing K/64 (got T=%d splits=%d)",
                 T, splits);
     const int pdl = (flags & ATX_FLAG_PDL) ? 1 : 0;
-    // per-call L2 prefetch depth (k-blocks) in bits 8..15 of flags overrides the process-wide default
-    tl_l2_prefetch_kb = ((flags >> 8) & 0xff) ? ((flags >> 8) & 0xff) : g_l2_prefetch_kb;
     const int kmode = mode | (ordered ? 0x100 : 0);
     if (T <= 16) return launch_gemm<16>(p, 0, out, ldo, T, kmode, splits, pdl, stream);
     if (T <= 32) return launch_gemm<32>(p, 1, out, ldo, T, kmode, splits, pdl, stream);

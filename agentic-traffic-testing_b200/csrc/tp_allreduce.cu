@@ -4,18 +4,15 @@
 // o_proj / down_proj -> NCCL all-reduce -> residual add -> RMSNorm (transformers modeling_llama.py:313-332
 // for the add + norm). At decode sizes the message is tiny ([tokens, hidden] fp32: 1 MiB at 32 tokens of a
 // 70B model) and 160 of them per step are pure latency. Here the collective, the add and the norm are ONE
-// kernel over NVLink peer memory:
-//
-//   every rank's GEMM accumulates its partial projection into its own symmetric buffer `part`;
-//   this kernel 1) tells every peer "my partial is complete" and waits for the same from all of them
-//   (release/acquire flags in peer memory), 2) each CTA pulls one token row from ALL ranks' buffers with
-//   16-byte peer loads, adds them to the local fp32 residual row, 3) writes the residual back and the
-//   bf16 RMS-normalised row for the next GEMM, 4) clears the OTHER of the two ping-pong partial buffers
-//   (every peer finished reading it: they could not have signalled this round otherwise).
-//
-// One-shot (every rank pulls everything) is latency-optimal for the <= 256-token steps this is used for;
-// prefill-sized steps keep NCCL's bandwidth-optimal ring. Ranks must be one process per GPU: the flag
-// wait spins on values that only the peers' kernels write.
+// kernel over NVLink peer memory, in two forms (both two-shot: rank r owns the token rows t = r mod world):
+//   * <= 64 rows: the low-latency push form (atx_allreduce_add_rmsnorm_ll): no flag exchange at all, the data
+//     is the flag (sentinel-filled receive slots), one NVLink one-way latency per phase: 11 us per call;
+//   * <= 256 rows: the flag-barrier form (atx_reduce_scatter_rmsnorm_all_gather): release/acquire flags in peer
+//     memory, pulls of the owned rows, peer stores of the normalised bf16 rows: 22 us per call;
+// prefill-sized steps keep NCCL's bandwidth-optimal ring. A one-shot form (every rank pulls everything, one
+// cluster per row) was measured at 12 us per call and 8.9 ms per 70B step against 6.3 with the push form and is
+// gone (profiles/r01k, r01m). Ranks must be one process per GPU: the waits spin on values that only the peers'
+// kernels write.
 #include "common.cuh"
 
 #include "../../include/atx_b200.h"
@@ -25,11 +22,6 @@ namespace atx {
 constexpr int kArThreads = 512;
 constexpr int kArMaxCluster = 8;   // CTAs per token row, one float4 per thread -> H <= 16384
 constexpr int kArMaxRanks = 8;
-
-struct ArArgs {
-    const float* part[kArMaxRanks];   // every rank's active partial buffer (peer-mapped), [T, H]
-    int* flags[kArMaxRanks];          // every rank's flag array (peer-mapped), int[world]
-};
 
 __device__ __forceinline__ void st_release_sys(int* p, int v) {
     asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
@@ -58,110 +50,6 @@ __device__ __forceinline__ float ar_dsmem_ld(const float* local_ptr, uint32_t ct
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(smem_u32(local_ptr)), "r"(cta_rank));
     asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(remote) : "memory");
     return v;
-}
-
-// A token row is split over a cluster of C CTAs (C = H / 2048, so a thread owns ONE float4 of the row): all of
-// a thread's peer loads (world of them) are issued back to back and the whole [T, H] x world message is in
-// flight in a single NVLink round trip instead of one round trip per 2048 columns. The row's sum of squares
-// crosses the cluster through distributed shared memory.
-__global__ void __launch_bounds__(kArThreads)
-allreduce_add_rmsnorm_kernel(ArArgs a, float* __restrict__ x, float* __restrict__ clear_buf, int clear_rows,
-                             int* __restrict__ state, int rank, int world, const int* __restrict__ rows,
-                             const uint2* __restrict__ w, uint2* __restrict__ out, int T, int H, float eps,
-                             uint4* __restrict__ zero_ptr, long long zero_vecs, int C) {
-    __shared__ float red[kArThreads / 32];
-    __shared__ float css;   // this CTA's share of the row's sum of squares
-    pdl_launch_dependents();
-    pdl_wait();  // this rank's own GEMM has finished adding into its partial buffer
-    const int epoch = *reinterpret_cast<volatile int*>(state) + 1;  // same in every CTA: bumped by the last CTA out
-    const int t = blockIdx.x / C, c = blockIdx.x % C;   // cluster = the C CTAs of one row
-    if (t >= T) {
-        const long long nb = gridDim.x - static_cast<long long>(T) * C;
-        for (long long i = (static_cast<long long>(blockIdx.x) - static_cast<long long>(T) * C) * blockDim.x + threadIdx.x;
-             i < zero_vecs; i += nb * blockDim.x)
-            zero_ptr[i] = make_uint4(0, 0, 0, 0);
-    } else {
-        // ---- cross-GPU barrier: announce, then wait for every rank's announcement of this round
-        if (blockIdx.x == 0 && threadIdx.x < world) {
-            __threadfence_system();
-            st_release_sys(a.flags[threadIdx.x] + rank, epoch);
-        }
-        if (threadIdx.x < world) {
-            const int* f = a.flags[rank] + threadIdx.x;
-            while (ld_acquire_sys(f) < epoch) {
-            }
-        }
-        __syncthreads();
-
-        const int r = rows ? rows[t] : t;
-        const int nv = H / 4, per = (nv + C - 1) / C;
-        const int i = c * per + threadIdx.x;
-        const bool ok = threadIdx.x < per && i < nv;
-        float4* xr = reinterpret_cast<float4*>(x + static_cast<long long>(r) * H);
-        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-        float ss = 0.f;
-        if (ok) {
-            float4 q[kArMaxRanks];
-#pragma unroll
-            for (int p = 0; p < kArMaxRanks; ++p)
-                if (p < world) q[p] = ld_peer_f4(a.part[p] + static_cast<long long>(r) * H + 4 * i);
-            acc = xr[i];
-#pragma unroll
-            for (int p = 0; p < kArMaxRanks; ++p) {   // fixed rank order: every rank computes the same sum
-                if (p < world) {
-                    acc.x += q[p].x; acc.y += q[p].y; acc.z += q[p].z; acc.w += q[p].w;
-                }
-            }
-            if (!rows) xr[i] = acc;  // the residual stream now includes the reduced projection
-            ss = acc.x * acc.x + acc.y * acc.y + acc.z * acc.z + acc.w * acc.w;
-        }
-        ss = warp_sum(ss);
-        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            float tot = 0.f;
-#pragma unroll
-            for (int k = 0; k < kArThreads / 32; ++k) tot += red[k];
-            css = tot;
-        }
-        float tot;
-        if (C > 1) {
-            ar_cluster_barrier();
-            tot = 0.f;
-            for (int k = 0; k < C; ++k) tot += ar_dsmem_ld(&css, static_cast<uint32_t>(k));
-        } else {
-            __syncthreads();
-            tot = css;
-        }
-        const float rs = rsqrtf(tot / static_cast<float>(H) + eps);
-        if (ok) {
-            const uint2 wv = __ldg(w + i);
-            uint2 o;
-            o.x = pack_bf16(bf16lo(wv.x) * (acc.x * rs), bf16hi(wv.x) * (acc.y * rs));
-            o.y = pack_bf16(bf16lo(wv.y) * (acc.z * rs), bf16hi(wv.y) * (acc.w * rs));
-            out[static_cast<long long>(t) * nv + i] = o;
-        }
-        // the other ping-pong buffer was fully read by every peer in the previous round: hand it back clean
-        if (clear_buf) {
-            const long long cv = static_cast<long long>(clear_rows) * nv;
-            float4* cb = reinterpret_cast<float4*>(clear_buf);
-            for (long long k = static_cast<long long>(blockIdx.x) * kArThreads + threadIdx.x; k < cv;
-                 k += static_cast<long long>(T) * C * kArThreads)
-                cb[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-        }
-        if (C > 1) ar_cluster_barrier();   // peers may still be reading css
-    }
-    // ---- last CTA out publishes the round number for the next call
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        __threadfence();
-        const int prev = atomicAdd(state + 1, 1);
-        if (prev == static_cast<int>(gridDim.x) - 1) {
-            state[1] = 0;
-            __threadfence();
-            *reinterpret_cast<volatile int*>(state) = epoch;
-        }
-    }
 }
 
 // ---- two-shot variant: reduce-scatter by token row, RMSNorm on the owner, all-gather of the bf16 result ----
@@ -474,57 +362,6 @@ allreduce_ll_kernel(LlArgs a, float* __restrict__ x, const float* __restrict__ p
 using namespace atx;
 
 extern "C" {
-
-int atx_allreduce_add_rmsnorm(float* x, const void* const* part_ptrs, void* const* flag_ptrs, void* clear_buf,
-                              int clear_rows, int* state, int rank, int world, const int* rows, const void* w,
-                              void* out, int T, int H, float eps, void* zero_ptr, long long zero_bytes, int flags,
-                              atx_stream_t stream) {
-    ATX_REQUIRE(x && part_ptrs && flag_ptrs && state && w && out, "atx_allreduce_add_rmsnorm: null pointer");
-    ATX_REQUIRE(world >= 2 && world <= kArMaxRanks && rank >= 0 && rank < world,
-                "atx_allreduce_add_rmsnorm: world=%d (2..%d), rank=%d", world, kArMaxRanks, rank);
-    ATX_REQUIRE(T > 0 && H > 0 && H % 4 == 0 && H <= kArThreads * kArMaxCluster * 4,
-                "atx_allreduce_add_rmsnorm: bad shape T=%d H=%d (H %% 4 == 0, H <= %d)", T, H,
-                kArThreads * kArMaxCluster * 4);
-    ATX_REQUIRE(zero_bytes >= 0 && zero_bytes % 16 == 0 && (zero_bytes == 0 || zero_ptr),
-                "atx_allreduce_add_rmsnorm: zero_bytes=%lld must be a non-negative multiple of 16 with a buffer",
-                zero_bytes);
-    ArArgs a = {};
-    for (int p = 0; p < world; ++p) {
-        ATX_REQUIRE(part_ptrs[p] && flag_ptrs[p], "atx_allreduce_add_rmsnorm: null peer pointer for rank %d", p);
-        a.part[p] = static_cast<const float*>(part_ptrs[p]);
-        a.flags[p] = static_cast<int*>(flag_ptrs[p]);
-    }
-    const long long zv = zero_bytes / 16;
-    long long zb = (zv + kArThreads * 8 - 1) / (kArThreads * 8);
-    if (zb > 1024) zb = 1024;
-    int C = 1;   // power of two so that the cluster shape is portable
-    while (C * kArThreads * 4 < H) C *= 2;
-    cudaLaunchConfig_t cfg = {};
-    cudaLaunchAttribute attr[2];
-    int na = 0;
-    if (flags & ATX_FLAG_PDL) {
-        attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-        attr[na].val.programmaticStreamSerializationAllowed = 1;
-        ++na;
-    }
-    if (C > 1) {
-        attr[na].id = cudaLaunchAttributeClusterDimension;
-        attr[na].val.clusterDim.x = static_cast<unsigned>(C);
-        attr[na].val.clusterDim.y = 1;
-        attr[na].val.clusterDim.z = 1;
-        ++na;
-    }
-    cfg.attrs = attr;
-    cfg.numAttrs = na;
-    zb = (zb + C - 1) / C;   // zeroing CTAs come in whole clusters too
-    cfg.gridDim = dim3(static_cast<unsigned>((T + zb) * C));
-    cfg.blockDim = dim3(kArThreads);
-    cfg.stream = reinterpret_cast<cudaStream_t>(stream);
-    ATX_CUDA(cudaLaunchKernelEx(&cfg, allreduce_add_rmsnorm_kernel, a, x, static_cast<float*>(clear_buf), clear_rows,
-                                state, rank, world, rows, reinterpret_cast<const uint2*>(w),
-                                reinterpret_cast<uint2*>(out), T, H, eps, reinterpret_cast<uint4*>(zero_ptr), zv, C));
-    return ATX_OK;
-}
 
 int atx_reduce_scatter_rmsnorm_all_gather(float* x, const void* const* part_ptrs, void* const* flag_ptrs,
                                           void* const* out_ptrs, void* clear_buf, int clear_rows, int* state, int rank,

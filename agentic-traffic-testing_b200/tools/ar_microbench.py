@@ -1,6 +1,5 @@
 """Latency of the tensor-parallel all-reduce + residual add + RMSNorm step alone (no GEMMs between), per mode:
 
-    fused    atx_allreduce_add_rmsnorm              one-shot over peer memory
     sharded  atx_reduce_scatter_rmsnorm_all_gather  two-shot (reduce-scatter by row, all-gather by peer stores)
     nccl     dist.all_reduce + atx_rmsnorm(add=)    NCCL over NVLink + the local add/norm kernel
     ll       atx_allreduce_add_rmsnorm_ll           push protocol, the data is the flag (run last: it arms xn)
@@ -77,11 +76,7 @@ def main() -> None:
         st = torch.cuda.current_stream().cuda_stream
         for k in range(a.n):
             b = k % 2
-            if mode == "fused":
-                ck(lib.atx_allreduce_add_rmsnorm(x.data_ptr(), parts[b], fl, part[1 - b].data_ptr(), T, state.data_ptr(),
-                                                 rank, world, None, w.data_ptr(), xn[0].data_ptr(), T, H, 1e-5, None, 0,
-                                                 _cabi.FLAG_PDL, st))
-            elif mode == "sharded":
+            if mode == "sharded":
                 ck(lib.atx_reduce_scatter_rmsnorm_all_gather(x.data_ptr(), parts[b], fl, outs, part[1 - b].data_ptr(), T,
                                                              state.data_ptr(), rank, world, None, w.data_ptr(), T, H,
                                                              1e-5, None, 0, _cabi.FLAG_PDL, st))
@@ -95,7 +90,7 @@ def main() -> None:
                                    None, 0, _cabi.FLAG_PDL, st))
 
     res = {}
-    for mode in ("fused", "sharded", "nccl", "ll"):
+    for mode in ("sharded", "nccl", "ll"):
         with torch.cuda.stream(stream):
             if mode == "ll":   # the other modes left plain data in the activation buffers: arm them
                 xn.view(torch.int16).fill_(-32768)

@@ -355,7 +355,7 @@ def cpu_config1(threads: int) -> dict:
             "host_dram_gbs": round(wbytes / 1e9 * 63 / dec, 1)}
 
 
-def tp70b_measure(dist, rank, world, local, pk, steps, warmup, out_tokens=256, layers=None, prefetch_ab=""):
+def tp70b_measure(dist, rank, world, local, pk, steps, warmup, out_tokens=256, layers=None):
     """BASELINE.json configs[3]: Llama-3.1-70B sharded tensor-parallel over the `world` GPUs of the box (one rank
     per GPU, schedulers in lockstep), agent fan-out batch 32. Returns the record (value = output tokens/s)."""
     import numpy as np
@@ -406,22 +406,8 @@ def tp70b_measure(dist, rank, world, local, pk, steps, warmup, out_tokens=256, l
     dec = [(a.elapsed_time(b), ctx) for (a, b, nd, npf, ctx) in evs if npf == 0 and nd == B]
     ms = max_over_ranks(dist, [sum(d[0] for d in dec) / len(dec)], "cuda")[0]
     out = {}
-    # optional A/B inside the same process (an 8-GPU box is expensive to bring up twice): decode step time
-    # with the post-all-reduce GEMMs prefetching `kb` weight slices into L2 while they wait
-    ab = {}
-    for kb in [int(v) for v in prefetch_ab.split(",") if v.strip()]:
-        r.tp_l2_prefetch_kb = kb
-        r.close()                      # drop the captured graphs: they bake the flag in
-        one(2000 + kb)
-        _, ev2 = one(3000 + kb)
-        d2 = [a.elapsed_time(b) for (a, b, nd, npf, ctx) in ev2 if npf == 0 and nd == B]
-        ab[str(kb)] = round(max_over_ranks(dist, [sum(d2) / len(d2)], "cuda")[0], 3)
-    if ab:
-        out["tp_l2_prefetch_ab_decode_step_ms"] = ab
     byts = (mcfg.weight_bytes_per_decode_step() + mcfg.kv_bytes_per_token() * (sum(d[1] for d in dec) / len(dec))) / world
-    mode = ("ll: push protocol, data is the flag (atx_allreduce_add_rmsnorm_ll)" if r.ll_ar else
-            "sharded: flag barrier + reduce-scatter/all-gather kernel" if r.sharded_ar else
-            "fused: flag barrier + one-shot kernel" if r.fused_ar else "nccl")
+    mode = "ll: push protocol, data is the flag (atx_allreduce_add_rmsnorm_ll)" if r.fused_ar else "nccl"
     out.update({"metric": "Llama-3.1-70B tensor-parallel decode tokens/s + p50 TTFT under agent fan-out",
                 "value": round(steps * B * O / wall, 1), "unit": UNIT, "steps": steps, "warmup": warmup,
                 "ms_per_step": round(1e3 * wall / steps, 1),
@@ -634,8 +620,7 @@ def run_other_workload(args, rank, world, local):
                                            f"(chunked prefill, 8192-token budget) + {O} greedy tokens over paged KV",
                                "parallelism": "1 GPU", "kv_blocks": r.num_blocks}})
     elif args.workload == "tp70b":
-        out.update(tp70b_measure(dist, rank, world, local, pk, args.steps, args.warmup, args.tp_out, args.layers,
-                                 args.tp_prefetch_ab))
+        out.update(tp70b_measure(dist, rank, world, local, pk, args.steps, args.warmup, args.tp_out, args.layers))
         if rank == 0:
             print(json.dumps(out), flush=True)
         if dist is not None:
@@ -668,8 +653,6 @@ def main() -> None:
     ap.add_argument("--long-out", type=int, default=128)
     ap.add_argument("--tp-out", type=int, default=256)
     ap.add_argument("--layers", type=int, default=None, help="tp70b / --impl reference: reduce depth for smoke runs")
-    ap.add_argument("--tp-prefetch-ab", default="", help="tp70b only: comma-separated ATX_TP_L2_PREFETCH_KB values "
-                                                         "to time after the main measurement")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

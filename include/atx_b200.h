@@ -36,9 +36,6 @@ typedef void* atx_stream_t; /* a cudaStream_t */
  * thread-block cluster reduced through distributed shared memory, one CTA adds each output element) instead
  * of letting every split race its red.add: results are bit-reproducible run to run; splits become 1/2/4/8. */
 #define ATX_FLAG_ORDERED 2
-/* atx_gemm_run only: prefetch this many 16 KB weight slices per CTA into L2 before waiting for the
- * upstream kernel (useful for a GEMM that sits behind a long non-GEMM chain, e.g. o_proj behind attention) */
-#define ATX_FLAG_L2_PREFETCH(kb) (((kb) & 0xff) << 8)
 
 /* Thread-local text of the last error raised on the calling thread. Never NULL. */
 const char* atx_last_error(void);
@@ -68,9 +65,6 @@ void atx_gemm_plan_destroy(atx_gemm_plan* plan);
 int atx_gemm_run(const atx_gemm_plan* plan, void* out, long long ldo, int T, int mode, int splits,
                  int flags, atx_stream_t stream);
 int atx_gemm_auto_splits(long long N, long long K, int T);
-/* Tuning knob: how many 16 KB weight slices a CTA launched with ATX_FLAG_PDL prefetches into L2
- * before it waits for the upstream kernel (default 0 = off: it measured slower on B200). Process-wide. */
-void atx_gemm_set_l2_prefetch(int k_blocks);
 
 /* ---- embedding gather: out[t, :] = float(table[ids[t], :]) ---------------------------------------
  * Replaces LlamaModel.embed_tokens (modeling_llama.py:375-427). table: [V, H] bf16, out fp32. */
@@ -90,24 +84,20 @@ int atx_rmsnorm(float* x, float* add, const int* rows, const void* w, void* out,
  * Replaces the NCCL all-reduce vLLM issues after o_proj / down_proj of a tensor-parallel Llama layer
  * (the reference reaches it through llm/serve_llm.py:374-379) together with the residual add and
  * LlamaRMSNorm that follow (modeling_llama.py:313-332, 62-67). One process per GPU; every rank calls
- * it with the same T.  part_ptrs[p] / flag_ptrs[p] (HOST arrays of `world` device pointers) are rank
- * p's partial-sum buffer [T, H] fp32 and flag array int[world], both mapped into this process
- * (symmetric / IPC memory).  x += sum_p part_p (written back unless `rows` gathers), out = bf16 norm.
- * clear_buf (nullable): the OTHER ping-pong partial buffer of this rank, first clear_rows rows are
+ * it with the same T. Two forms, both two-shot with rank r owning the token rows t = r (mod world).
+ *
+ * Flag-barrier form (up to 256 rows).  part_ptrs[p] / flag_ptrs[p] (HOST arrays of `world` device pointers) are
+ * rank p's partial-sum buffer [T, H] fp32 and flag array int[2 * world], both mapped into this process (symmetric /
+ * IPC memory).  x fp32 is the residual stream, w the bf16 norm weight, `rows` (nullable) gathers rows before
+ * the norm.  clear_buf (nullable): the OTHER ping-pong partial buffer of this rank, first clear_rows rows are
  * zeroed after the cross-GPU barrier.  state: int[2] in local device memory, zero-initialised once.
- * zero_ptr / zero_bytes as in atx_rmsnorm. */
-int atx_allreduce_add_rmsnorm(float* x, const void* const* part_ptrs, void* const* flag_ptrs, void* clear_buf,
-                              int clear_rows, int* state, int rank, int world, const int* rows, const void* w,
-                              void* out, int T, int H, float eps, void* zero_ptr, long long zero_bytes, int flags,
-                              atx_stream_t stream);
-
-/* Two-shot variant of the above for larger worlds: rank r owns the token rows t = r (mod world). It pulls
- * only those rows of every peer's partial buffer, keeps the fp32 residual of its own rows in x (rows it does
+ * zero_ptr / zero_bytes as in atx_rmsnorm.  The rank pulls
+ * only its own rows of every peer's partial buffer, keeps the fp32 residual of its own rows in x (rows it does
  * not own go stale: x must not be read whole between calls), and writes the normalised bf16 rows into EVERY
  * rank's activation buffer through out_ptrs[p] (HOST array of `world` peer-mapped device pointers to the same
  * [T, H] bf16 buffer on each rank). A second cross-GPU barrier inside the kernel keeps it running until
  * every peer's rows have arrived here, so the consumer only needs stream order. flag_ptrs[p] must hold
- * int[2 * world]. NVLink bytes per rank: (world-1)/world * T*H*6 instead of (world-1) * T*H*4. */
+ * int[2 * world]. NVLink bytes per rank: (world-1)/world * T*H*6. */
 int atx_reduce_scatter_rmsnorm_all_gather(float* x, const void* const* part_ptrs, void* const* flag_ptrs,
                                           void* const* out_ptrs, void* clear_buf, int clear_rows, int* state, int rank,
                                           int world, const int* rows, const void* w, int T, int H, float eps,
@@ -123,7 +113,7 @@ int atx_reduce_scatter_rmsnorm_all_gather(float* x, const void* const* part_ptrs
  *               when the call starts
  *   reset_ptr / reset_bytes  LOCAL region filled with the bf16 sentinel: the OTHER parity's activation rows,
  *               which the GEMMs before this call have finished reading (16-byte multiple)
- *   clear_buf / clear_rows, zero_ptr / zero_bytes, rows, x, w  as in atx_allreduce_add_rmsnorm (local housekeeping)
+ *   clear_buf / clear_rows, zero_ptr / zero_bytes, rows, x, w  as in the flag-barrier form (local housekeeping)
  * Calls must alternate between two parities (two rs / out buffer sets), every rank making the same calls in
  * the same order. The whole grid (T x ceil(H/2048) CTAs) spins on remote data and must be co-resident: rejected
  * otherwise. Latency per call, 1 MiB message: see profiles/ (ar_microbench). */

@@ -92,3 +92,6 @@ if __name__ == "__main__":
     # of the tcgen05 attention): what __graft_entry__.smoke() runs. Prompt seed 55 was picked among 23..62 as the
     # one whose 32-token greedy path has the largest minimum top-1/top-2 margin (0.15) in the fp32 oracle
     make("tiny128", seed=21, prompt_seed=55, prompt_len=232, new_tokens=32, out=gold / "hf_tiny128_long.npz")
+    # the same for the head_dim-64 shape with TWO KV heads (it shards over 2 GPUs: tests/test_gpu_tp.py runs its
+    # 200-row prefill chunk through the flag-barrier all-reduce). Prompt seed 97: margin 0.118, best of 70..109
+    make("tiny", seed=11, prompt_seed=97, prompt_len=200, new_tokens=32, out=gold / "hf_tiny_long.npz")

@@ -44,7 +44,8 @@ def _run_collect(eng, prompt, n_new, temperature=0.0):
 
 
 @pytest.mark.parametrize("shape_name,gold,seed", [("tiny", "hf_tiny.npz", 11), ("tiny128", "hf_tiny128.npz", 21),
-                                                  ("tiny128", "hf_tiny128_long.npz", 21)])
+                                                  ("tiny128", "hf_tiny128_long.npz", 21),
+                                                  ("tiny", "hf_tiny_long.npz", 11)])
 @pytest.mark.parametrize("graphs", [False, True])
 def test_greedy_and_logits_against_hf_golden(shape_name, gold, seed, graphs):
     g = np.load(GOLD / gold)

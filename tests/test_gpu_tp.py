@@ -13,7 +13,7 @@ pytestmark = pytest.mark.gpu
 GOLD = Path(__file__).parent / "golden"
 
 
-def _rank(rank, world, port, graphs, mode, q, temperature=0.0, n_new=16):
+def _rank(rank, world, port, graphs, mode, q, temperature=0.0, n_new=16, fixture=("tiny", "hf_tiny.npz", 11)):
     import sys
 
     root = Path(__file__).resolve().parent.parent
@@ -27,17 +27,20 @@ def _rank(rank, world, port, graphs, mode, q, temperature=0.0, n_new=16):
     from oracle import llama_ref as R
 
     os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
-    os.environ["ATX_TP_ALLREDUCE"] = mode
     torch.cuda.set_device(rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     try:
-        g = np.load(GOLD / "hf_tiny.npz")
-        shape, mcfg = R.shape_by_name("tiny"), model_config_by_name("tiny")
-        sd = R.init_weights(shape, 11)
+        shape_name, gold, seed = fixture
+        g = np.load(GOLD / gold)
+        shape, mcfg = R.shape_by_name(shape_name), model_config_by_name(shape_name)
+        sd = R.init_weights(shape, seed)
         w = ModelWeights.from_state_dict(mcfg, sd, torch.device("cuda", rank), world, rank)
+        long_prompt = len(g["prompt"]) > 64       # one prefill chunk of 65..256 rows: the flag-barrier all-reduce
         eng = LLMEngine(ModelSource(mcfg, None, None),
-                        EngineConfig(max_model_len=256, max_num_seqs=4, max_num_batched_tokens=64, num_gpu_blocks=32,
-                                     device=rank, tp_size=world, tp_rank=rank, enable_cuda_graphs=graphs), w)
+                        EngineConfig(max_model_len=512 if long_prompt else 256, max_num_seqs=4,
+                                     max_num_batched_tokens=256 if long_prompt else 64, num_gpu_blocks=64,
+                                     device=rank, tp_size=world, tp_rank=rank, enable_cuda_graphs=graphs,
+                                     tp_allreduce=mode), w)
         seq = eng.add_request("tp", g["prompt"].tolist(), SamplingParams(temperature=temperature, max_tokens=n_new,
                                                                          ignore_eos=True))
         eng.step()
@@ -55,14 +58,17 @@ def _rank(rank, world, port, graphs, mode, q, temperature=0.0, n_new=16):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("mode", ["ll", "fused", "sharded", "nccl"])
+FIXTURES = {"short": ("tiny", "hf_tiny.npz", 11), "long": ("tiny", "hf_tiny_long.npz", 11)}
+
+
+@pytest.mark.parametrize("prompt", ["short", "long"])
+@pytest.mark.parametrize("mode", ["auto", "nccl"])
 @pytest.mark.parametrize("graphs", [False, True])
-def test_tp2_matches_hf_golden(graphs, mode):
-    """mode 'fused': all-reduce + residual add + RMSNorm in one kernel over NVLink peer memory
-    (atx_allreduce_add_rmsnorm); mode 'sharded': its two-shot form, reduce-scatter by token row + norm on the
-    owner + all-gather by peer stores (atx_reduce_scatter_rmsnorm_all_gather); mode 'll': the same data flow
-    pushed, with the data as the flag (atx_allreduce_add_rmsnorm_ll); mode 'nccl': NCCL all-reduce + fused
-    add/norm kernel."""
+def test_tp2_matches_hf_golden(graphs, mode, prompt):
+    """mode 'auto': all-reduce + residual add + RMSNorm in one kernel over NVLink peer memory — the push form with
+    the data as the flag for steps of up to 64 rows (atx_allreduce_add_rmsnorm_ll: the short prompt's prefill and
+    every decode step), the flag-barrier form for up to 256 rows (atx_reduce_scatter_rmsnorm_all_gather: the
+    200-token prompt's prefill chunk); mode 'nccl': NCCL all-reduce + fused add/norm kernel."""
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     with socket.socket() as s:
@@ -70,11 +76,11 @@ def test_tp2_matches_hf_golden(graphs, mode):
         port = s.getsockname()[1]
     ctx = tmp.get_context("spawn")
     q = ctx.Queue()
-    procs = [ctx.Process(target=_rank, args=(r, 2, port, graphs, mode, q)) for r in range(2)]
+    procs = [ctx.Process(target=_rank, args=(r, 2, port, graphs, mode, q, 0.0, 16, FIXTURES[prompt])) for r in range(2)]
     for p in procs:
         p.start()
     try:
-        got = sorted(q.get(timeout=240) for _ in procs)
+        got = sorted(q.get(timeout=120) for _ in procs)
         for p in procs:
             p.join(timeout=60)
             assert p.exitcode == 0
@@ -82,9 +88,9 @@ def test_tp2_matches_hf_golden(graphs, mode):
         for p in procs:  # never leave a rank behind holding a GPU
             if p.is_alive():
                 p.kill()
-    gold = np.load(GOLD / "hf_tiny.npz")["greedy"][:16].tolist()
+    gold = np.load(GOLD / FIXTURES[prompt][1])["greedy"][:16].tolist()
     (r0, e0, ids0, ar0, f0), (r1, e1, ids1, ar1, f1) = got
-    print(f"\n[tp2 graphs={graphs} {mode}] logits max-abs vs HF fp32: rank0 {e0:.4f} rank1 {e1:.4f}; all-reduces {ar0}; "
+    print(f"\n[tp2 graphs={graphs} {mode} {prompt}] logits max-abs vs HF fp32: rank0 {e0:.4f} rank1 {e1:.4f}; all-reduces {ar0}; "
           f"fused kernel active: {f0}")
     assert f0 == f1 == (mode != "nccl")
     assert ids0 == ids1 == gold           # both ranks sample the same tokens, equal to HF greedy
@@ -102,7 +108,7 @@ def _run_pair(args):
     for p in procs:
         p.start()
     try:
-        got = sorted(q.get(timeout=240) for _ in procs)
+        got = sorted(q.get(timeout=120) for _ in procs)
         for p in procs:
             p.join(timeout=60)
             assert p.exitcode == 0
@@ -119,7 +125,7 @@ def test_tp2_ranks_sample_identically_at_the_reference_temperature():
     on both ranks, and equal again after a restart (fresh processes, different str-hash salts)."""
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
-    runs = [_run_pair((True, "ll", 0.2, 64)) for _ in range(2)]
+    runs = [_run_pair((True, "auto", 0.2, 64)) for _ in range(2)]
     for (r0, _, ids0, _, _), (r1, _, ids1, _, _) in runs:
         assert len(ids0) == 64 and ids0 == ids1
     assert runs[0][0][2] == runs[1][0][2]

@@ -13,10 +13,10 @@ from oracle.kv_ref import RefPagedKV, capacity_gauges
 GOLD = Path(__file__).parent / "golden"
 
 
-@pytest.mark.parametrize("name,seed", [("tiny", 11), ("tiny128", 21), ("tiny128_long", 21)])
+@pytest.mark.parametrize("name,seed", [("tiny", 11), ("tiny128", 21), ("tiny128_long", 21), ("tiny_long", 11)])
 def test_restatement_reproduces_hf_golden(name, seed):
     g = np.load(GOLD / f"hf_{name}.npz")
-    name = name.replace("_long", "")   # the 232-token prompt on the head_dim-128 fixture (what smoke() runs)
+    name = name.replace("_long", "")   # long prompts: 232 tokens on the head_dim-128 fixture (what smoke() runs), 200 on tiny
     shape = R.shape_by_name(name)
     w = R.init_weights(shape, seed)
     ref = R.RefLlama(shape, w)
