@@ -364,6 +364,35 @@ def test_paged_prefill_attention(cabi, Hq, Hkv, D):
         assert torch.all(err <= 2 ** -6 * want.abs() + 6e-3), (i, float(err.max()))
 
 
+@pytest.mark.parametrize("Hq,Hkv,D", [(8, 1, 128), (4, 1, 64)])
+def test_paged_prefill_attention_tile_edges(cabi, Hq, Hkv, D):
+    """Sizes around the kernel's tiling: 128-row query tiles in pairs (one tile only, a second tile with one row),
+    128-key K/V tiles handed over in 64-key halves (a half that is fully masked or past the context, contexts
+    ending on and next to page / half / tile boundaries, tile B seeing one key tile more than tile A), GQA groups
+    of 8 (70B) and 4, chunk offsets on and off a tile boundary."""
+    cases = [(1, 1), (63, 63), (64, 1), (65, 65), (127, 127), (128, 128), (129, 129), (192, 64), (255, 255),
+             (256, 256), (257, 257), (300, 44), (513, 385), (1000, 1000), (70, 3), (384, 128), (385, 129)]
+    lens = [c for c, _ in cases]
+    kc, vc, bt, ks, vs = _paged_case(7 + D, lens, Hq, Hkv, D)
+    g = torch.Generator().manual_seed(79)
+    nq = [n for _, n in cases]
+    cu = [0]
+    for n in nq:
+        cu.append(cu[-1] + n)
+    T = cu[-1]
+    q = _bf16(torch.randn(T, Hq, D, generator=g))
+    out = torch.full((T, Hq * D), float("nan"), dtype=torch.bfloat16, device="cuda")
+    cabi.paged_attn_prefill(q.cuda().view(T, Hq * D), kc.cuda(), vc.cuda(), bt.cuda(),
+                            torch.tensor(cu, dtype=torch.int32).cuda(), torch.tensor(lens, dtype=torch.int32).cuda(),
+                            out, len(cases), max(nq), Hq, Hkv, D, 16, D ** -0.5)
+    got = out.float().cpu().view(T, Hq, D)
+    assert torch.isfinite(got).all()
+    for i, (ctx, n) in enumerate(cases):
+        want = R.attention(q[cu[i]:cu[i + 1]].float(), ks[i], vs[i], ctx - n)
+        err = (got[cu[i]:cu[i + 1]] - want).abs()
+        assert torch.all(err <= 2 ** -6 * want.abs() + 6e-3), ((ctx, n), float(err.max()))
+
+
 # ------------------------------------------------------------------------------------- sampler
 def test_argmax_exact_and_tie_break(cabi):
     g = torch.Generator().manual_seed(1)
