@@ -18,7 +18,7 @@ Layer schedule (per token batch of T rows; h is the fp32 residual stream):
   xn = rmsnorm(h); act = swiglu(xn @ Wgu^T) (GEMM epilogue, bf16); h += act @ Wdown^T
 Tensor parallel (tp_size > 1): the two `h +=` projections produce partial sums, and the all-reduce, the
 residual add and the following rmsnorm are ONE kernel of ours over NVLink peer memory (`_fused_norm`:
-low-latency push form for decode-sized steps, flag-barrier forms up to 256 rows, NCCL beyond).
+low-latency push form for decode-sized steps, flag-barrier form up to 256 rows, NCCL beyond).
 """
 from __future__ import annotations
 
