@@ -156,7 +156,8 @@ def _tp_rank_main(rank, world, port, out_q):
         part_logits = xn @ w.lm_head.float().T                              # vocabulary shard
         all_logits = [torch.zeros_like(part_logits) for _ in range(world)]
         dist.all_gather(all_logits, part_logits)
-        out_q.put((rank, torch.cat(all_logits, dim=1)))
+        # by value (numpy): a torch tensor would travel as a shared-memory handle that dies with this process
+        out_q.put((rank, torch.cat(all_logits, dim=1).numpy()))
     finally:
         dist.destroy_process_group()
 
@@ -174,7 +175,7 @@ def test_tp_data_flow_gloo_world2_matches_unsharded_oracle():
     procs = [ctx.Process(target=_tp_rank_main, args=(r, 2, port, q)) for r in range(2)]
     for p in procs:
         p.start()
-    got = dict(q.get(timeout=180) for _ in procs)
+    got = {r: torch.from_numpy(a) for r, a in (q.get(timeout=180) for _ in procs)}
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
