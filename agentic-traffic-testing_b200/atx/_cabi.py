@@ -21,6 +21,7 @@ GEMM_STORE_BF16 = 2
 GEMM_SWIGLU_BF16 = 3
 FLAG_PDL = 1
 FLAG_ORDERED = 2   # atx_gemm_run ADD_F32, T <= 64: fixed-order split-K (bit-reproducible)
+FLAG_ADD_BF16 = 4  # atx_rmsnorm: the `add` buffer is bf16
 
 EXPORTS = [
     "atx_last_error", "atx_version", "atx_device_info",

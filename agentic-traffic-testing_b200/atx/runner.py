@@ -84,6 +84,8 @@ class ModelRunner:
         self.attn = torch.zeros(T, q_size, dtype=bf, device=dev)
         self.act = torch.zeros(T, I, dtype=bf, device=dev)
         self.part = torch.zeros(T, H, dtype=f32, device=dev) if tp > 1 else None  # partial o/down sums (TP)
+        # ... of prefill-sized steps: stored and all-reduced in bf16 (half the NCCL bytes; what vLLM reduces too)
+        self.part_bf = torch.zeros(T, H, dtype=bf, device=dev) if tp > 1 else None
         self.allreduce_calls = 0
         self.fused_ar = False      # all-reduce + add + norm in our own kernels over peer memory (else: NCCL + norm kernel)
         self.xn = self.xn2 = self.xl = None
@@ -216,13 +218,18 @@ class ModelRunner:
             # steps that took another path may have left plain data in the first activation buffer: re-arm it
             # (the other one and xl are re-armed by the first all-reduce call below)
             self._arm_a.fill_(-32768)
+        bf_part = False
         if tp == 1:
             targets = (h, h)                      # projections add straight into the residual stream
         elif fused:
             targets = (self.sym_part[0].data_ptr(), self.sym_part[1].data_ptr())
         else:
-            self.part[:T].zero_()
-            targets = (self.part.data_ptr(),) * 2
+            # NCCL path. Decode-sized steps accumulate split-K partials in fp32; beyond 64 rows the GEMM is the
+            # persistent kernel (no split-K), which stores its tile once: bf16, then a bf16 all-reduce
+            bf_part = T > 64
+            if not bf_part:
+                self.part[:T].zero_()
+            targets = (self.part_bf.data_ptr() if bf_part else self.part.data_ptr(),) * 2
         n = 0
         k = 0            # index of the next projection whose partial sum needs reducing (TP)
         pending = None   # None | buffer index (fused) | True (NCCL-reduced partial waiting in self.part)
@@ -232,21 +239,27 @@ class ModelRunner:
             if tp > 1 and fused and pending is not None:
                 self._fused_norm(pending, T, w_ptr, out_ptr, rows_ptr, rows_n, zero_ptr, zero_bytes, st)
             else:
-                add = self.part.data_ptr() if (tp > 1 and pending is not None) else None
-                ck(lib.atx_rmsnorm(h, add, rows_ptr, w_ptr, out_ptr, rows_n, H, m.rms_norm_eps, zero_ptr, zero_bytes, fl,
+                add, afl = None, fl
+                if tp > 1 and pending is not None:
+                    add = self.part_bf.data_ptr() if bf_part else self.part.data_ptr()
+                    afl = fl | (_cabi.FLAG_ADD_BF16 if bf_part else 0)
+                ck(lib.atx_rmsnorm(h, add, rows_ptr, w_ptr, out_ptr, rows_n, H, m.rms_norm_eps, zero_ptr, zero_bytes, afl,
                                    st))
             n += 1
 
         def project(plan) -> None:
             """o_proj / down_proj: accumulate into the residual (tp 1) or into this round's partial buffer."""
             nonlocal n, k, pending
-            ck(lib.atx_gemm_run(plan._h, targets[k % 2], H, T, _cabi.GEMM_ADD_F32, 0, fl, st))
+            if bf_part:
+                ck(lib.atx_gemm_run(plan._h, targets[0], H, T, _cabi.GEMM_STORE_BF16, 1, fl, st))
+            else:
+                ck(lib.atx_gemm_run(plan._h, targets[k % 2], H, T, _cabi.GEMM_ADD_F32, 0, fl, st))
             n += 1
             if tp > 1:
                 if fused:
                     pending = k % 2
                 else:
-                    self._all_reduce(self.part[:T])
+                    self._all_reduce(self.part_bf[:T] if bf_part else self.part[:T])
                     pending = True
                 k += 1
 

@@ -32,7 +32,7 @@ constexpr int kNormMaxVec = 8;  // float4 per thread -> H <= 8192
 __global__ void __launch_bounds__(kNormThreads)
 rmsnorm_kernel(float* __restrict__ x, float* __restrict__ add, const int* __restrict__ rows,
                const uint2* __restrict__ w, uint2* __restrict__ out, int T, int H, float eps,
-               uint4* __restrict__ zero_ptr, long long zero_vecs) {
+               uint4* __restrict__ zero_ptr, long long zero_vecs, int add_bf16) {
     __shared__ float red[kNormThreads / 32];
     pdl_launch_dependents();
     pdl_wait();
@@ -47,7 +47,10 @@ rmsnorm_kernel(float* __restrict__ x, float* __restrict__ add, const int* __rest
     const int t = blockIdx.x;
     const int r = rows ? rows[t] : t;
     float4* xr = reinterpret_cast<float4*>(x + static_cast<long long>(r) * H);
-    float4* ar = add ? reinterpret_cast<float4*>(add + static_cast<long long>(r) * H) : nullptr;
+    float4* ar = (add && !add_bf16) ? reinterpret_cast<float4*>(add + static_cast<long long>(r) * H) : nullptr;
+    // ATX_FLAG_ADD_BF16: the partial projection was all-reduced in bf16 (prefill-sized tensor-parallel steps, as
+    // vLLM does for every step): read only, nothing to hand back cleared
+    const uint2* ab = (add && add_bf16) ? reinterpret_cast<const uint2*>(add) + static_cast<long long>(r) * (H / 4) : nullptr;
     const int nv = H / 4;
     float4 v[kNormMaxVec];
     float ss = 0.f;
@@ -65,6 +68,11 @@ rmsnorm_kernel(float* __restrict__ x, float* __restrict__ add, const int* __rest
                     xr[i] = v[j];
                     ar[i] = make_float4(0.f, 0.f, 0.f, 0.f);
                 }
+            }
+            if (ab) {
+                const uint2 a = ab[i];
+                v[j].x += bf16lo(a.x); v[j].y += bf16hi(a.x); v[j].z += bf16lo(a.y); v[j].w += bf16hi(a.y);
+                if (!rows) xr[i] = v[j];
             }
             ss += v[j].x * v[j].x + v[j].y * v[j].y + v[j].z * v[j].z + v[j].w * v[j].w;
         }
@@ -208,7 +216,8 @@ int atx_rmsnorm(float* x, float* add, const int* rows, const void* w, void* out,
     cfg.stream = reinterpret_cast<cudaStream_t>(stream);
     set_pdl(cfg, attr, flags);
     ATX_CUDA(cudaLaunchKernelEx(&cfg, rmsnorm_kernel, x, add, rows, reinterpret_cast<const uint2*>(w),
-                                reinterpret_cast<uint2*>(out), T, H, eps, reinterpret_cast<uint4*>(zero_ptr), zv));
+                                reinterpret_cast<uint2*>(out), T, H, eps, reinterpret_cast<uint4*>(zero_ptr), zv,
+                                (flags & ATX_FLAG_ADD_BF16) ? 1 : 0));
     return ATX_OK;
 }
 

@@ -36,6 +36,8 @@ typedef void* atx_stream_t; /* a cudaStream_t */
  * thread-block cluster reduced through distributed shared memory, one CTA adds each output element) instead
  * of letting every split race its red.add: results are bit-reproducible run to run; splits become 1/2/4/8. */
 #define ATX_FLAG_ORDERED 2
+/* atx_rmsnorm only: `add` points to bf16 [T, H] instead of fp32 (a partial projection all-reduced in bf16) */
+#define ATX_FLAG_ADD_BF16 4
 
 /* Thread-local text of the last error raised on the calling thread. Never NULL. */
 const char* atx_last_error(void);
@@ -75,7 +77,8 @@ int atx_embed_gather(const int* ids, const void* table, float* out, int T, int H
  * Replaces LlamaRMSNorm.forward (modeling_llama.py:62-67) and, with `add`, the residual add before it
  * (LlamaDecoderLayer.forward :313-332). x fp32 (the residual stream), w bf16, out bf16.
  * add (nullable, fp32 [T, H]): x[r, :] += add[r, :] first; without `rows` the sum is written back to x
- * and add is cleared (tensor parallelism: add = all-reduced partial o_proj / down_proj output).
+ * and add is cleared (tensor parallelism: add = all-reduced partial o_proj / down_proj output). With
+ * ATX_FLAG_ADD_BF16, add is bf16 [T, H] and is left as it is.
  * Optionally zero-fills `zero_ptr[0 .. zero_bytes)` (16-byte multiple) for a following split-K GEMM. */
 int atx_rmsnorm(float* x, float* add, const int* rows, const void* w, void* out, int T, int H, float eps,
                 void* zero_ptr, long long zero_bytes, int flags, atx_stream_t stream);
