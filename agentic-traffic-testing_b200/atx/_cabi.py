@@ -161,7 +161,8 @@ def rmsnorm(x: torch.Tensor, w: torch.Tensor, out: torch.Tensor, T: int, eps: fl
             rows: Optional[torch.Tensor] = None, zero: Optional[torch.Tensor] = None, zero_bytes: int = 0,
             flags: int = 0, add: Optional[torch.Tensor] = None) -> None:
     _dev(x, w, out, rows, zero, add)
-    assert add is None or (add.dtype == torch.float32 and add.shape[-1] == x.shape[-1])
+    assert add is None or (add.shape[-1] == x.shape[-1] and
+                           add.dtype == (torch.bfloat16 if flags & FLAG_ADD_BF16 else torch.float32))
     assert x.dtype == torch.float32 and w.dtype == torch.bfloat16 and out.dtype == torch.bfloat16
     if zero is not None and zero_bytes == 0:
         zero_bytes = zero.numel() * zero.element_size()

@@ -205,6 +205,33 @@ def test_rmsnorm(cabi, T, H):
     assert torch.all(zero == 0)
 
 
+@pytest.mark.parametrize("rows", [False, True])
+def test_rmsnorm_residual_add_fp32_and_bf16(cabi, rows):
+    """Tensor-parallel residual: x += add before the norm. fp32 add (decode-sized steps: split-K partials, handed back
+    cleared) and bf16 add (ATX_FLAG_ADD_BF16: prefill-sized steps all-reduce in bf16; left untouched). With a row
+    gather nothing is written back."""
+    g = torch.Generator().manual_seed(31)
+    T, H = 12, 4096
+    x0 = torch.randn(T, H, generator=g) * 2
+    a0 = torch.randn(T, H, generator=g)
+    w = _bf16(1 + 0.1 * torch.randn(H, generator=g))
+    idx = torch.tensor([11, 0, 5], dtype=torch.int32) if rows else None
+    n = 3 if rows else T
+    sel = idx.long() if rows else torch.arange(T)
+    for flag, add0 in ((0, a0), (cabi.FLAG_ADD_BF16, _bf16(a0))):
+        x, add = x0.cuda(), add0.cuda()
+        out = torch.empty(n, H, dtype=torch.bfloat16, device="cuda")
+        cabi.rmsnorm(x, w.cuda(), out, n, 1e-5, rows=idx.cuda() if rows else None, add=add, flags=flag)
+        summed = x0[sel] + add0.float()[sel]
+        want = R.rms_norm(summed, w.float(), 1e-5)
+        assert torch.all((out.float().cpu() - want).abs() <= 2 ** -8 * want.abs() + 1e-6)
+        if rows:
+            assert torch.equal(x.cpu(), x0) and torch.equal(add.cpu(), add0)
+        else:
+            assert torch.equal(x.cpu(), summed)                                  # residual written back
+            assert torch.equal(add.cpu(), add0 if flag else torch.zeros(T, H))   # fp32 buffer handed back cleared
+
+
 def test_rmsnorm_row_gather(cabi):
     g = torch.Generator().manual_seed(9)
     x = torch.randn(20, 512, generator=g)
