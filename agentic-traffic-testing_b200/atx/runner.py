@@ -405,6 +405,48 @@ class ModelRunner:
                 self.flags, st))
         self.allreduce_calls += 1
 
+    def allreduce_alone_us(self, T: int, n_calls: int, reps: int = 10) -> Optional[float]:
+        """Bench hook (BASELINE configs[3] asks for the all-reduce share of a step): the all-reduce + residual add +
+        RMSNorm calls of one T-row step back to back with nothing between them, captured as one CUDA graph and
+        replayed; microseconds per call on this rank. Every rank of the group must call it. The residual stream is
+        left meaningless (call it between requests only)."""
+        if not (self.tp > 1 and self.fused_ar and T <= self.FUSED_AR_MAX_T) or n_calls % 2:
+            return None
+        import torch.distributed as dist
+
+        ln = self.w.layers[0].ln1.data_ptr()
+
+        def body() -> None:
+            st = torch.cuda.current_stream().cuda_stream
+            self._ll_now = T <= self.LL_AR_MAX_T
+            if self._ll_now:
+                self._arm_a.fill_(-32768)
+            for k in range(n_calls):      # the parities alternate exactly as in a step: o_proj -> xn2, down_proj -> xn
+                self._fused_norm(k % 2, T, ln, (self.xn2 if k % 2 == 0 else self.xn).data_ptr(), None, T, None, 0, st)
+
+        s = torch.cuda.Stream(device=self.dev)
+        torch.cuda.synchronize(self.dev)
+        dist.barrier(group=self.tp_group)
+        with torch.cuda.stream(s):
+            body()
+            s.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=s, capture_error_mode="thread_local"):
+                body()
+            g.replay()
+            s.synchronize()
+            dist.barrier(group=self.tp_group)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(reps):
+                g.replay()
+            e1.record()
+            s.synchronize()
+        us = e0.elapsed_time(e1) * 1e3 / (reps * n_calls)
+        del g
+        torch.cuda.synchronize(self.dev)
+        return us
+
     def _all_reduce(self, t: torch.Tensor) -> None:
         import torch.distributed as dist
 

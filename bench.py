@@ -407,6 +407,11 @@ def tp70b_measure(dist, rank, world, local, pk, steps, warmup, out_tokens=256, l
     ms = max_over_ranks(dist, [sum(d[0] for d in dec) / len(dec)], "cuda")[0]
     out = {}
     byts = (mcfg.weight_bytes_per_decode_step() + mcfg.kv_bytes_per_token() * (sum(d[1] for d in dec) / len(dec))) / world
+    # the step's all-reduce + add + norm calls alone (nothing between them): their share of the step if none of it
+    # were hidden; inside the step the GEMM behind each call prefetches its weights meanwhile
+    n_ar = 2 * mcfg.num_hidden_layers
+    ar_us = r.allreduce_alone_us(B, n_ar)
+    ar_us = max_over_ranks(dist, [ar_us or 0.0], "cuda")[0]
     mode = "ll: push protocol, data is the flag (atx_allreduce_add_rmsnorm_ll)" if r.fused_ar else "nccl"
     out.update({"metric": "Llama-3.1-70B tensor-parallel decode tokens/s + p50 TTFT under agent fan-out",
                 "value": round(steps * B * O / wall, 1), "unit": UNIT, "steps": steps, "warmup": warmup,
@@ -417,6 +422,8 @@ def tp70b_measure(dist, rank, world, local, pk, steps, warmup, out_tokens=256, l
                                 "frac": round(byts / ms / 1e6 / pk["hbm_gbs"], 4),
                                 "decode_tokens_per_s": round(B / ms * 1e3, 1),
                                 "allreduces_per_step": 2 * mcfg.num_hidden_layers + 1,
+                                "allreduce_alone_us_per_call": round(ar_us, 2) if ar_us else None,
+                                "allreduce_alone_share_of_step": round(n_ar * ar_us / 1e3 / ms, 4) if ar_us else None,
                                 "allreduce_message_bytes": B * mcfg.hidden_size * 4},
                 "gpu_launches": r.kernel_launches - l0,
                 "tp_allreduce": mode,
