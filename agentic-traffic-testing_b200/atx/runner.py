@@ -194,8 +194,9 @@ class ModelRunner:
         Tensor parallel (tp > 1, Megatron split: q/k/v/gate/up by output features = heads, o/down by
         input features): o_proj and down_proj produce PARTIAL sums. For decode-sized steps the
         all-reduce, the residual add and the following RMSNorm are one kernel over NVLink peer memory
-        (atx_allreduce_add_rmsnorm, ping-pong symmetric buffers); prefill-sized steps use NCCL's ring and
-        fold the reduced partial into the residual inside the RMSNorm kernel (`add`). The LM head is
+        (atx_allreduce_add_rmsnorm_ll up to 64 rows, atx_reduce_scatter_rmsnorm_all_gather up to 256; ping-pong
+        symmetric buffers); prefill-sized steps store the partial in bf16, all-reduce it with NCCL's ring and fold it
+        into the residual inside the RMSNorm kernel (`add`). The LM head is
         vocabulary-parallel: each rank computes its column slice of the logits, reduces every row of it to one
         (score, global index) pair (atx_sample_shard: arg-max, or Gumbel-max keyed by the global index), the ranks
         exchange the pairs (8 bytes per row and rank, one NCCL all-gather) and pick the best (atx_sample_merge):
